@@ -1,0 +1,271 @@
+"""Generate golden vectors by importing the UNMODIFIED reference.
+
+Run in the build container only (needs /root/reference; the GPU box has none):
+
+    python tests/golden/make_golden.py
+
+Writes ``tests/golden/ref_*.npz``.  Everything the reference computes here is
+driven with injected parameters (never through its k-means RNG).
+The files are small and committed; tests read them and never the reference.
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+
+REF = os.environ.get("DGMM_REFERENCE", "/root/reference")
+sys.path.insert(0, REF)
+warnings.filterwarnings("ignore")
+
+from deconv.gmm.deconv_gmm import DeconvGMM  # noqa: E402
+from deconv.gmm.online_deconv_gmm import OnlineDeconvGMM  # noqa: E402
+from deconv.gmm.batch_deconv_gmm import BatchDeconvGMM  # noqa: E402
+from deconv.gmm.sgd_deconv_gmm import SGDDeconvGMM  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def synth(rng, N, D, K, noise_scale=0.5, spread=3.0):
+    """Synthetic mixture + per-point full noise in the style of
+    experiments/gmm/checks/data.py:5-10 (smaller spread so that
+    responsibilities are not all one-hot)."""
+    mu = rng.uniform(-spread, spread, size=(K, D))
+    q = rng.standard_normal((K, D, D))
+    Sigma = np.einsum("kba,kbc->kac", q, q) + 0.1 * np.eye(D)
+    alpha = rng.dirichlet(np.ones(K) * 3.0)
+    qn = noise_scale * rng.standard_normal((N, D, D))
+    S = np.einsum("nba,nbc->nac", qn, qn) + 1e-3 * np.eye(D)
+    comp = rng.integers(0, K, size=N)
+    X = np.empty((N, D))
+    for i in range(N):
+        X[i] = rng.multivariate_normal(mu[comp[i]], Sigma[comp[i]] + S[i])
+    return X, S, alpha, mu, Sigma
+
+
+def inject(model, alpha, mu, Sigma, dtype):
+    model.weights = torch.tensor(alpha, dtype=dtype)[:, None]
+    model.means = torch.tensor(mu, dtype=dtype)
+    model.covars = torch.tensor(Sigma, dtype=dtype)
+    model.w = model.w.to(dtype)
+
+
+def em_case(name, rng, N, D, K, dtype, w=1e-3, iters=(1, 3)):
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    torch.set_default_dtype(dtype)
+    m = DeconvGMM(K, D, w=w)
+    inject(m, alpha, mu, Sigma, dtype)
+    data = (torch.tensor(X, dtype=dtype), torch.tensor(S, dtype=dtype))
+    ll, (log_r, b, B) = m._e_step(data)
+    out = dict(X=X, S=S, alpha=alpha, mu=mu, Sigma=Sigma, w=w,
+               ll_sum=ll.item(), log_resps=log_r.numpy(), cond_means=b.numpy(),
+               cond_covars=B.numpy())
+    m._m_step(data, (log_r, b, B))
+    out.update(m1_weights=m.weights.numpy().copy(), m1_means=m.means.numpy().copy(),
+               m1_covars=m.covars.numpy().copy())
+    # further full EM iterations (E then M), recording params after each count
+    done = 1
+    for target in iters:
+        while done < target:
+            _, e = m._e_step(data)
+            m._m_step(data, e)
+            done += 1
+        out["it%d_weights" % target] = m.weights.numpy().copy()
+        out["it%d_means" % target] = m.means.numpy().copy()
+        out["it%d_covars" % target] = m.covars.numpy().copy()
+        out["it%d_ll" % target] = m._e_step(data)[0].item()
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, "ll_sum", out["ll_sum"])
+
+
+def sgd_case(name, rng, N, D, K, dtype):
+    X, S, _, mu, _ = synth(rng, N, D, K)
+    torch.set_default_dtype(dtype)
+    m = SGDDeconvGMM(K, D, w=1e-3, batch_size=16)
+    sw = rng.standard_normal(K)
+    l_diag = 0.3 * rng.standard_normal((K, D))
+    l_lower = 0.5 * rng.standard_normal((K, D * (D - 1) // 2))
+    m.module.soft_weights.data = torch.tensor(sw, dtype=dtype)
+    m.module.means.data = torch.tensor(mu, dtype=dtype)
+    m.module.l_diag.data = torch.tensor(l_diag, dtype=dtype)
+    m.module.l_lower.data = torch.tensor(l_lower, dtype=dtype)
+    data = (torch.tensor(X, dtype=dtype), torch.tensor(S, dtype=dtype))
+    g = rng.standard_normal(N)
+    ll = m.module(data)
+    (ll * torch.tensor(g, dtype=dtype)).sum().backward()
+    out = dict(X=X, S=S, soft_weights=sw, means=mu, l_diag=l_diag, l_lower=l_lower, g=g,
+               ll=ll.detach().numpy(),
+               d_soft_weights=m.module.soft_weights.grad.numpy().copy(),
+               d_means=m.module.means.grad.numpy().copy(),
+               d_l_diag=m.module.l_diag.grad.numpy().copy(),
+               d_l_lower=m.module.l_lower.grad.numpy().copy(),
+               covars=m.covars.numpy().copy(),
+               reg_loss=m.reg_loss(16, 64).item())
+    with torch.no_grad():
+        pw, pm, pc = m.posterior_params(data)
+    out.update(post_log_w=pw.numpy(), post_means=pm.numpy(), post_covars=pc.numpy())
+    # the training objective of sgd_gmm.py:173-181 on this one batch
+    for p in m.module.parameters():
+        p.grad = None
+    lp = m.module(data)
+    loss = -1 * torch.mean(lp) + m.reg_loss(N, 4 * N)
+    loss.backward()
+    out.update(loss=loss.item(),
+               loss_d_soft_weights=m.module.soft_weights.grad.numpy().copy(),
+               loss_d_means=m.module.means.grad.numpy().copy(),
+               loss_d_l_diag=m.module.l_diag.grad.numpy().copy(),
+               loss_d_l_lower=m.module.l_lower.grad.numpy().copy())
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, "ll mean", out["ll"].mean())
+
+
+def online_batch_case(name, rng, N, D, K, dtype):
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    torch.set_default_dtype(dtype)
+    w = 1e-3
+    on = OnlineDeconvGMM(K, D, w=w, batch_size=N, step_size=0.1)
+    inject(on, alpha, mu, Sigma, dtype)
+    on.sum_resps = on.weights * on.batch_size
+    on.sum_cond_means = on.means * on.sum_resps
+    data = (torch.tensor(X, dtype=dtype), torch.tensor(S, dtype=dtype))
+    ll, e = on._e_step(data)
+    on._m_step(e, N, 0.1)
+    out = dict(X=X, S=S, alpha=alpha, mu=mu, Sigma=Sigma, w=w, step_size=0.1,
+               eps=float(torch.finfo(dtype).eps),
+               on_weights=on.weights.numpy().copy(), on_means=on.means.numpy().copy(),
+               on_covars=on.covars.numpy().copy(), on_sum_resps=on.sum_resps.numpy().copy(),
+               on_sum_cond_means=on.sum_cond_means.numpy().copy(), ll_sum=ll.item())
+    # second online step on the same batch from the updated state
+    ll2, e2 = on._e_step(data)
+    on._m_step(e2, N, 0.1)
+    out.update(on2_weights=on.weights.numpy().copy(), on2_means=on.means.numpy().copy(),
+               on2_covars=on.covars.numpy().copy(), ll2_sum=ll2.item())
+
+    bt = BatchDeconvGMM(K, D, w=w, batch_size=N)
+    inject(bt, alpha, mu, Sigma, dtype)
+    half = N // 2
+    parts = [(data[0][:half], data[1][:half]), (data[0][half:], data[1][half:])]
+    sr = torch.zeros(K, 1)
+    sm = torch.zeros(K, D)
+    tl = 0.0
+    for p in parts:
+        lp, (a, b) = bt._step_1(p)
+        sr += a
+        sm += b
+        tl += lp.item()
+    new_means = sm / sr
+    sc = torch.zeros(K, D, D)
+    for p in parts:
+        sc += bt._step_2(p, new_means)
+    out.update(bt_ll=tl, bt_sum_resps=sr.numpy().copy(), bt_sum_cond_means=sm.numpy().copy(),
+               bt_sum_cond_covars=sc.numpy().copy(),
+               bt_weights=(sr / N).numpy().copy(), bt_means=new_means.numpy().copy(),
+               bt_covars=((sc + 2 * bt.w) / sr[:, :, None]).numpy().copy())
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, "online ll", out["ll_sum"], "batch ll", tl)
+
+
+def data_gen_case(name):
+    """deconv/utils/data_gen.py fixture (seeds :42,:63): mean ll under the
+    generating mixture, plus a 512-point slice with per-point values."""
+    from deconv.utils.data_gen import generate_mixture_data
+    from deconv.gmm.sgd_deconv_gmm import SGDDeconvDataset
+    torch.set_default_dtype(torch.float32)
+    gmm, S, (z_tr, x_tr), (z_va, x_va), (z_te, x_te) = generate_mixture_data()
+    x_tr, x_va, x_te = x_tr[0], x_va[0], x_te[0]   # minibatch_sample adds a leading 1
+    out = {}
+    for tag, x in (("train", x_tr), ("val", x_va), ("test", x_te)):
+        ds = SGDDeconvDataset(x, S.repeat(x.shape[0], 1, 1))
+        out["mean_ll_" + tag] = gmm.score_batch(ds) / x.shape[0]
+        out["n_" + tag] = x.shape[0]
+    sl = slice(0, 512)
+    Sx = S.repeat(512, 1, 1)
+    with torch.no_grad():
+        ll = gmm.module((x_te[sl], Sx))
+        pw, pm, pc = gmm.posterior_params((x_te[sl], Sx))
+    out.update(x_test=x_te[sl].numpy(), S=S.numpy(), ll_test=ll.numpy(),
+               soft_weights=gmm.module.soft_weights.detach().numpy(),
+               means=gmm.module.means.detach().numpy(),
+               l_diag=gmm.module.l_diag.detach().numpy(),
+               l_lower=gmm.module.l_lower.detach().numpy(),
+               post_log_w=pw.numpy(), post_means=pm.numpy(), post_covars=pc.numpy())
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, {k: v for k, v in out.items() if k.startswith("mean_ll")})
+
+
+def robustness_case(name):
+    """huge / tiny noise stays finite in the fp32 reference."""
+    torch.set_default_dtype(torch.float32)
+    K, D = 3, 2
+    alpha = np.full(K, 1.0 / 3)
+    mu = np.array([[0.0, 0.0], [2.0, 3.0], [2.0, -3.0]])
+    Sigma = np.array([np.diag([0.1, 1.5]), np.diag([1.0, 0.1]), np.diag([1.0, 0.1])])
+    X = np.array([[0.5, 0.25], [2.0, 2.5], [-1.0, 4.0], [0.1, -0.2]])
+    S = np.array([np.diag([1e12, 1e-2]), 1e-4 * np.eye(2), np.diag([1e-2, 1e12]),
+                  np.array([[2.0, -0.5], [-0.5, 1.0]])])
+    m = DeconvGMM(K, D)
+    inject(m, alpha, mu, Sigma, torch.float32)
+    ll, (lr, b, B) = m._e_step((torch.tensor(X, dtype=torch.float32), torch.tensor(S, dtype=torch.float32)))
+    np.savez_compressed(os.path.join(HERE, name), X=X, S=S, alpha=alpha, mu=mu, Sigma=Sigma,
+                        ll_sum=ll.item(), log_resps=lr.numpy(), cond_means=b.numpy(),
+                        cond_covars=B.numpy())
+    print(name, ll.item(), np.isfinite(B.numpy()).all())
+
+
+def boston_case(name):
+    """BASELINE.json configs[0]: boston (506x11), K=10, synthetic per-point
+    diagonal noise, injected init, a few full EM iterations (float64)."""
+    dtype = torch.float64
+    torch.set_default_dtype(dtype)
+    rng = np.random.default_rng(20260101)
+    X0 = np.load(os.path.join(REF, "data_small", "boston_no_discrete.npy"))
+    N, D = X0.shape
+    K = 10
+    var = 0.1 * (0.5 + rng.uniform(size=(N, D)))
+    X = X0 + np.sqrt(var) * rng.standard_normal((N, D))
+    S = np.zeros((N, D, D))
+    S[:, np.arange(D), np.arange(D)] = var
+    rows = rng.choice(N, size=K, replace=False)
+    alpha = np.full(K, 1.0 / K)
+    mu = X[rows].copy()
+    Sigma = np.tile(np.eye(D), (K, 1, 1))
+    m = DeconvGMM(K, D, w=1e-3)
+    inject(m, alpha, mu, Sigma, dtype)
+    data = (torch.tensor(X), torch.tensor(S))
+    out = dict(noise_var=var, X=X, rows=rows, w=1e-3)
+    lls = []
+    for it in range(1, 11):
+        ll, e = m._e_step(data)
+        lls.append(ll.item())
+        m._m_step(data, e)
+        if it in (1, 5, 10):
+            out["it%d_weights" % it] = m.weights.numpy().copy()
+            out["it%d_means" % it] = m.means.numpy().copy()
+            out["it%d_covars" % it] = m.covars.numpy().copy()
+    out["ll_trace"] = np.asarray(lls)
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, lls[0], lls[-1])
+
+
+def main():
+    rng = np.random.default_rng(12345)
+    em_case("ref_em_d3_k4_f64.npz", rng, N=40, D=3, K=4, dtype=torch.float64)
+    em_case("ref_em_d10_k6_f64.npz", rng, N=24, D=10, K=6, dtype=torch.float64)
+    em_case("ref_em_d10_k6_f32.npz", rng, N=24, D=10, K=6, dtype=torch.float32)
+    em_case("ref_em_d16_k5_f64.npz", rng, N=12, D=16, K=5, dtype=torch.float64, iters=(1,))
+    sgd_case("ref_sgd_d4_k5_f64.npz", rng, N=30, D=4, K=5, dtype=torch.float64)
+    sgd_case("ref_sgd_d7_k3_f32.npz", rng, N=20, D=7, K=3, dtype=torch.float32)
+    online_batch_case("ref_online_batch_d3_k4_f64.npz", rng, N=32, D=3, K=4, dtype=torch.float64)
+    online_batch_case("ref_online_batch_d5_k3_f32.npz", rng, N=32, D=5, K=3, dtype=torch.float32)
+    data_gen_case("ref_data_gen.npz")
+    robustness_case("ref_robust_f32.npz")
+    boston_case("ref_boston_k10_f64.npz")
+
+
+if __name__ == "__main__":
+    main()
