@@ -1,0 +1,764 @@
+// dgmm_api.cu -- C ABI (include/dgmm_b200.h): argument checks, launch planning, the small
+// parameter-side kernels (prepare / finalise / M-step update / FP32 probe) and the
+// host-buffer streaming pipeline.  The hot kernels live in dgmm_pair*.cuh / dgmm_full*.cuh
+// and are reached through the per-D lookup functions of dgmm_tables.cuh.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "../../include/dgmm_b200.h"
+#include "dgmm_pair.cuh"
+#include "dgmm_full.cuh"
+
+// per-D lookup functions, one translation unit each (dgmm_inst_dXX.cu)
+#define DGMM_DECL(D)                                                       \
+    const void* dgmm_pair_lookup_d##D(int mode, int sigp, int accp, int rc); \
+    const void* dgmm_full_lookup_d##D();
+DGMM_DECL(1) DGMM_DECL(2) DGMM_DECL(3) DGMM_DECL(4) DGMM_DECL(5) DGMM_DECL(6) DGMM_DECL(7) DGMM_DECL(8)
+DGMM_DECL(9) DGMM_DECL(10) DGMM_DECL(11) DGMM_DECL(12) DGMM_DECL(13) DGMM_DECL(14) DGMM_DECL(15) DGMM_DECL(16)
+DGMM_DECL(17) DGMM_DECL(18) DGMM_DECL(19) DGMM_DECL(20) DGMM_DECL(21) DGMM_DECL(22) DGMM_DECL(23) DGMM_DECL(24)
+DGMM_DECL(25) DGMM_DECL(26) DGMM_DECL(27) DGMM_DECL(28) DGMM_DECL(29) DGMM_DECL(30) DGMM_DECL(31) DGMM_DECL(32)
+#undef DGMM_DECL
+
+namespace {
+
+using namespace dgmm;
+
+typedef const void* (*pair_lookup_t)(int, int, int, int);
+typedef const void* (*full_lookup_t)();
+
+#define DGMM_ROW(D) {dgmm_pair_lookup_d##D, dgmm_full_lookup_d##D}
+struct DimRow {
+    pair_lookup_t pair;
+    full_lookup_t full;
+};
+const DimRow kDims[DGMM_MAX_D + 1] = {
+    {nullptr, nullptr},
+    DGMM_ROW(1),  DGMM_ROW(2),  DGMM_ROW(3),  DGMM_ROW(4),  DGMM_ROW(5),  DGMM_ROW(6),  DGMM_ROW(7),  DGMM_ROW(8),
+    DGMM_ROW(9),  DGMM_ROW(10), DGMM_ROW(11), DGMM_ROW(12), DGMM_ROW(13), DGMM_ROW(14), DGMM_ROW(15), DGMM_ROW(16),
+    DGMM_ROW(17), DGMM_ROW(18), DGMM_ROW(19), DGMM_ROW(20), DGMM_ROW(21), DGMM_ROW(22), DGMM_ROW(23), DGMM_ROW(24),
+    DGMM_ROW(25), DGMM_ROW(26), DGMM_ROW(27), DGMM_ROW(28), DGMM_ROW(29), DGMM_ROW(30), DGMM_ROW(31), DGMM_ROW(32)};
+
+#define CUDA_TRY(x)                                  \
+    do {                                             \
+        cudaError_t e__ = (x);                       \
+        if (e__ != cudaSuccess) return (int)e__;     \
+    } while (0)
+
+struct DeviceInfo {
+    int device = -1, sms = 0, smem_optin = 0, cc_major = 0;
+};
+
+int device_info(DeviceInfo* out) {
+    static DeviceInfo cache[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return DGMM_ERR_NO_DEVICE;
+    if (dev < 0 || dev >= 64) return DGMM_ERR_NO_DEVICE;
+    if (cache[dev].device != dev) {
+        DeviceInfo d;
+        d.device = dev;
+        if (cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return DGMM_ERR_NO_DEVICE;
+        cudaDeviceGetAttribute(&d.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        cudaDeviceGetAttribute(&d.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+        if (d.cc_major != 10) return DGMM_ERR_NO_DEVICE;  // sm_100a cubins only
+        cache[dev] = d;
+    }
+    *out = cache[dev];
+    return 0;
+}
+
+inline size_t up256(size_t x) { return (x + 255) & ~(size_t)255; }
+inline int group_size(int K) {
+    if (K <= 32) {
+        int g = 1;
+        while (g < K) g <<= 1;
+        return g;
+    }
+    return (K + 31) & ~31;
+}
+inline int nd_of(int D) { return D * (D + 1) / 2; }
+inline int ns_of(int D) { return 1 + D + nd_of(D); }
+
+// Upper bound of the grid used for (D, K): shared by the workspace query and the launcher.
+inline int max_grid(int D, int K, int sms) {
+    (void)K;
+    const size_t per_block = (size_t)ns_of(D) * kPairMaxThreads * 4;  // a column per thread, worst case
+    size_t cap = ((size_t)256 << 20) / per_block;
+    size_t g = (size_t)sms * 8;
+    if (g > cap) g = cap;
+    if (g < (size_t)sms) g = sms;
+    return (int)g;
+}
+
+struct Workspace {
+    float* sig_cols;
+    float* mu_cols;
+    float* cj;
+    int* nonpd;
+    double* part_ll;
+    float* part;
+    size_t bytes;
+};
+
+Workspace carve(void* base, int D, int K, int sms) {
+    const int GS = group_size(K);
+    Workspace w;
+    size_t off = 0;
+    char* b = (char*)base;
+    w.sig_cols = (float*)(b + off); off += up256((size_t)nd_of(D) * GS * 4);
+    w.mu_cols = (float*)(b + off);  off += up256((size_t)D * GS * 4);
+    w.cj = (float*)(b + off);       off += up256((size_t)GS * 4);
+    w.nonpd = (int*)(b + off);      off += 256;
+    const int mg = max_grid(D, K, sms);
+    w.part_ll = (double*)(b + off); off += up256((size_t)mg * 2 * 8);
+    w.part = (float*)(b + off);     off += up256((size_t)mg * ns_of(D) * kPairMaxThreads * 4);
+    w.bytes = off;
+    return w;
+}
+
+// ---------------------------------------------------------------------------------------
+// small kernels
+// ---------------------------------------------------------------------------------------
+
+// Transposes the mixture parameters into per-thread columns:
+//   sig_cols[e][j] = lower(Sigma_j)[e] (+ shared noise), mu_cols[a][j], cj[j] = log alpha_j - D/2 log 2pi.
+// Padding components j >= K get Sigma = I, mu = 0, cj = -inf.
+__global__ void prepare_kernel(const float* __restrict__ log_alpha, const float* __restrict__ mu,
+                               const float* __restrict__ Sigma, const float* __restrict__ S_shared, int D,
+                               int K, int GS, float* __restrict__ sig_cols, float* __restrict__ mu_cols,
+                               float* __restrict__ cj, int* __restrict__ nonpd) {
+    const int ND = D * (D + 1) / 2;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nth = gridDim.x * blockDim.x;
+    if (tid == 0 && nonpd) *nonpd = 0;
+    for (int idx = tid; idx < ND * GS; idx += nth) {
+        const int e = idx / GS, j = idx - e * GS;
+        int a = 0;
+        while ((a + 1) * (a + 2) / 2 <= e) ++a;
+        const int b = e - a * (a + 1) / 2;
+        float v;
+        if (j < K) {
+            v = Sigma[((size_t)j * D + a) * D + b];
+            if (S_shared) v += S_shared[a * D + b];
+        } else {
+            v = (a == b) ? 1.f : 0.f;
+        }
+        sig_cols[idx] = v;
+    }
+    for (int idx = tid; idx < D * GS; idx += nth) {
+        const int a = idx / GS, j = idx - a * GS;
+        mu_cols[idx] = (j < K) ? mu[(size_t)j * D + a] : 0.f;
+    }
+    for (int j = tid; j < GS; j += nth) cj[j] = (j < K) ? (log_alpha[j] - D * kHalfLog2Pi) : -INFINITY;
+}
+
+// Sums the per-block partials (double accumulation, fixed order: deterministic) into the
+// packed statistics buffer.  beta = 1 accumulates onto the existing contents (host pipeline).
+__global__ void finalize_stats_kernel(const float* __restrict__ part, const double* __restrict__ part_ll,
+                                      const int* __restrict__ nonpd, int nblk, int D, int K, int GS, int cols,
+                                      int nslot, float* __restrict__ stats, int beta) {
+    const int ND = D * (D + 1) / 2, NS = 1 + D + ND;
+    const int per = 1 + D + D * D;
+    const int total = K * per;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid < total) {
+        // map output slot -> (j, packed element e)
+        int j, e, out;
+        if (tid < K) {
+            j = tid; e = 0; out = j;
+        } else if (tid < K + K * D) {
+            const int r = tid - K;
+            const int a = r / K; j = r - a * K;         // j fastest for coalesced partial reads
+            e = 1 + a; out = K + j * D + a;
+        } else {
+            const int r = tid - K - K * D;
+            const int ab = r / K; j = r - ab * K;
+            const int a = ab / D, b = ab - a * D;
+            const int hi = a > b ? a : b, lo = a > b ? b : a;
+            e = 1 + D + hi * (hi + 1) / 2 + lo;
+            out = K + K * D + (j * D + a) * D + b;
+        }
+        double s = 0.0;
+        // `cols` columns per block: GS when the block already summed its slots, TPB (= nslot * GS)
+        // when the accumulators are per-thread global columns
+        for (int blk = 0; blk < nblk; ++blk)
+            for (int sl = 0; sl < nslot; ++sl) s += (double)part[((size_t)blk * NS + e) * cols + sl * GS + j];
+        stats[out] = beta ? (stats[out] + (float)s) : (float)s;
+    } else if (tid == total) {
+        double ll = 0.0, sg = 0.0;
+        for (int blk = 0; blk < nblk; ++blk) { ll += part_ll[2 * blk]; sg += part_ll[2 * blk + 1]; }
+        float* tail = stats + total;
+        if (beta) ll += (double)tail[0] + (double)tail[1];
+        const float hi = (float)ll;
+        tail[0] = hi;
+        tail[1] = isfinite(hi) ? (float)(ll - (double)hi) : 0.f;
+        tail[2] = beta ? tail[2] + (float)sg : (float)sg;
+        tail[3] = beta ? tail[3] + (float)(*nonpd) : (float)(*nonpd);
+    }
+}
+
+__global__ void finalize_ll_kernel(const double* __restrict__ part_ll, const int* __restrict__ nonpd, int nblk,
+                                   double* __restrict__ out_sum, int* __restrict__ status, int beta) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        double ll = 0.0;
+        for (int blk = 0; blk < nblk; ++blk) ll += part_ll[2 * blk];
+        if (out_sum) {
+            out_sum[0] = beta ? out_sum[0] + ll : ll;
+            out_sum[1] = beta ? out_sum[1] + (double)(*nonpd) : (double)(*nonpd);
+        }
+        if (status) *status = *nonpd;
+    }
+}
+
+// Closed-form EM update from the packed statistics; one block per component, D*D threads.
+// deconv/gmm/deconv_gmm.py:81-109 via the identity of SURVEY.md Appendix C.
+__global__ void mstep_kernel(const float* __restrict__ stats, double n_total, double w, int D, int K,
+                             float* __restrict__ mu, float* __restrict__ Sigma, float* __restrict__ alpha,
+                             float* __restrict__ log_alpha) {
+    extern __shared__ double sh[];
+    double* Sg = sh;            // [D*D]
+    double* S2 = Sg + D * D;    // [D*D]
+    double* W = S2 + D * D;     // [D*D]  Sigma S2
+    double* v = W + D * D;      // [D]    Sigma s1
+    const int j = blockIdx.x;
+    const int t = threadIdx.x;
+    const int a = t / D, b = t - a * D;
+    const double s0 = (double)stats[j];
+    const float* s1 = stats + K + (size_t)j * D;
+    const float* s2 = stats + K + (size_t)K * D + (size_t)j * D * D;
+    float* Sj = Sigma + (size_t)j * D * D;
+    // the kernels only ever read the lower triangle; mirror it so that an asymmetric
+    // caller-supplied Sigma cannot leak into the update
+    Sg[t] = (double)Sj[a >= b ? a * D + b : b * D + a];
+    S2[t] = (double)s2[t];
+    __syncthreads();
+    double acc = 0.0;
+    for (int c = 0; c < D; ++c) acc += Sg[a * D + c] * S2[c * D + b];
+    W[t] = acc;
+    if (b == 0) {
+        double vv = 0.0;
+        for (int c = 0; c < D; ++c) vv += Sg[a * D + c] * (double)s1[c];
+        v[a] = vv;
+    }
+    __syncthreads();
+    double P = 0.0;
+    for (int c = 0; c < D; ++c) P += W[a * D + c] * Sg[c * D + b];
+    const double da = v[a] / s0, db = v[b] / s0;
+    double nv = Sg[t] + P / s0 - da * db;
+    if (a == b) nv += 2.0 * w / s0;
+    Sj[t] = (float)nv;
+    if (b == 0) mu[(size_t)j * D + a] = (float)((double)mu[(size_t)j * D + a] + da);
+    if (t == 0) {
+        const double al = s0 / n_total;
+        alpha[j] = (float)al;
+        log_alpha[j] = (float)log(al);
+    }
+}
+
+__global__ void log_kernel(const float* __restrict__ in, float* __restrict__ out, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = logf(in[i]);
+}
+
+// FP32 FMA probe: 8 independent chains per thread, register operands only.
+__global__ void __launch_bounds__(256) fp32_probe_kernel(float* sink, int iters) {
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f;
+    float a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float m = 0.999f + blockIdx.x * 1e-9f, c = 1e-3f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            a0 = fmaf(a0, m, c); a1 = fmaf(a1, m, c); a2 = fmaf(a2, m, c); a3 = fmaf(a3, m, c);
+            a4 = fmaf(a4, m, c); a5 = fmaf(a5, m, c); a6 = fmaf(a6, m, c); a7 = fmaf(a7, m, c);
+        }
+    }
+    const float s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (s == 123.456f) *sink = s;
+}
+
+// ---------------------------------------------------------------------------------------
+// launch planning for the pair kernel
+// ---------------------------------------------------------------------------------------
+struct Tuning {
+    int sigp = -1, accp = -1, nslot = -1, pt = -1, nst = -1, blocks_per_sm = -1, rc = -1, no_bulk = 0;
+};
+Tuning g_tuning;
+
+struct Plan {
+    const void* kernel = nullptr;
+    int sigp, accp, rc, GS, NSLOT, TPB, PT, NST, grid, use_bulk;
+    size_t smem;
+    long long n_tiles;
+};
+
+size_t pair_smem_bytes(int D, int noise, bool has_g, int sigp, int accp, int GS, int TPB, int PT, int NST,
+                       int mode) {
+    const StageLayout SL = stage_layout(D, noise, PT, has_g);
+    size_t b = kSmemHeader + (size_t)NST * SL.bytes;
+    if (sigp == ST_SMEM) b += (size_t)pad_col(nd_of(D)) * GS * 4;
+    if (mode == MODE_STATS && accp == ST_SMEM) b += (size_t)pad_col(ns_of(D)) * TPB * 4;
+    // the register-accumulator epilogue reuses the ring as TPB floats of scratch
+    if (b < kSmemHeader + (size_t)TPB * 4) b = kSmemHeader + (size_t)TPB * 4;
+    return b;
+}
+
+int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int noise, bool has_g,
+              const void* X, const void* S, const void* g, Plan* out) {
+    Plan p;
+    p.GS = group_size(K);
+    const Tuning& t = g_tuning;
+
+    // slots per block
+    if (p.GS <= 32) p.NSLOT = 128 / p.GS;
+    else p.NSLOT = std::max(1, 128 / p.GS);
+    if (t.nslot > 0) p.NSLOT = t.nslot;
+    if (p.GS > 32 && p.NSLOT > 15) p.NSLOT = 15;
+    while (p.GS * p.NSLOT > kPairMaxThreads) --p.NSLOT;
+    if (p.NSLOT < 1) return DGMM_ERR_UNSUPPORTED_K;
+
+    // placement of Sigma_j and of the accumulators
+    // (measured on B200, profiles/r01_variant_sweep.md)
+    if (D <= 12) { p.sigp = ST_SMEM; p.accp = ST_REG; p.rc = (mode == MODE_STATS) ? 1 : 2; }
+    else if (D <= DGMM_UNROLL_D) { p.sigp = (mode == MODE_STATS) ? ST_GLOBAL : ST_SMEM; p.accp = ST_SMEM; p.rc = 0; }
+    else { p.sigp = ST_GLOBAL; p.accp = ST_GLOBAL; p.rc = 0; }
+    if (t.sigp >= 0) p.sigp = t.sigp;
+    if (t.accp >= 0) p.accp = t.accp;
+    if (mode == MODE_LOGLIK) p.accp = ST_GLOBAL;
+    if (t.rc >= 0) p.rc = t.rc;
+
+    // tile size and ring depth
+    const int pt0 = (D <= 10) ? 16 : (D <= 16 ? 8 : 4);
+    p.NST = (D <= 16) ? 3 : 2;
+    if (t.nst > 0) p.NST = std::min(t.nst, kMaxStages);
+
+    for (int attempt = 0; attempt < 16; ++attempt) {
+        while (p.GS * p.NSLOT < 32) ++p.NSLOT;  // whole warps only (full-mask shuffles)
+        p.TPB = p.GS * p.NSLOT;
+        int PT = t.pt > 0 ? t.pt : pt0;
+        // PT must be a multiple of NSLOT and of 4
+        int lcm = p.NSLOT;
+        while (lcm % 4) lcm += p.NSLOT;
+        PT = ((PT + lcm - 1) / lcm) * lcm;
+        p.PT = PT;
+        p.smem = pair_smem_bytes(D, noise, has_g, p.sigp, p.accp, p.GS, p.TPB, p.PT, p.NST, mode);
+        if (p.smem <= (size_t)dev.smem_optin) break;
+        // does not fit: shrink in this order
+        if (p.NSLOT > 1 && p.GS >= 32) { p.NSLOT = 1; continue; }
+        if (p.GS < 32 && p.GS * p.NSLOT > 32) { p.NSLOT /= 2; continue; }
+        if (mode == MODE_STATS && p.accp == ST_SMEM) { p.accp = ST_GLOBAL; continue; }
+        if (p.sigp == ST_SMEM) { p.sigp = ST_GLOBAL; continue; }
+        if (p.NST > 1) { --p.NST; continue; }
+        return DGMM_ERR_UNSUPPORTED_K;
+    }
+    if (p.smem > (size_t)dev.smem_optin) return DGMM_ERR_UNSUPPORTED_K;
+
+    if (p.TPB > 128 && p.rc != 0) p.rc = 0;
+    p.kernel = kDims[D].pair(mode, p.sigp, p.accp, p.rc);
+    if (!p.kernel && p.rc != 0) { p.rc = 0; p.kernel = kDims[D].pair(mode, p.sigp, p.accp, 0); }
+    if (!p.kernel) {
+        // fall back to the universal placement (compiled for every D)
+        p.sigp = ST_GLOBAL;
+        if (mode == MODE_STATS) p.accp = ST_GLOBAL;
+        p.smem = pair_smem_bytes(D, noise, has_g, p.sigp, p.accp, p.GS, p.TPB, p.PT, p.NST, mode);
+        p.kernel = kDims[D].pair(mode, p.sigp, p.accp, 0);
+        if (!p.kernel) return DGMM_ERR_UNSUPPORTED_D;
+    }
+
+    CUDA_TRY(cudaFuncSetAttribute(p.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+    int occ = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, p.kernel, p.TPB, p.smem));
+    if (occ < 1) return DGMM_ERR_UNSUPPORTED_K;
+    if (t.blocks_per_sm > 0) occ = std::min(occ, t.blocks_per_sm);
+    p.n_tiles = (N + p.PT - 1) / p.PT;
+    long long grid = (long long)dev.sms * occ;
+    grid = std::min<long long>(grid, max_grid(D, K, dev.sms));
+    grid = std::min<long long>(grid, std::max<long long>(p.n_tiles, 1));
+    p.grid = (int)grid;
+
+    const bool aligned = (((uintptr_t)X | (uintptr_t)(noise == NOISE_FULL || noise == NOISE_DIAG ? S : nullptr) |
+                           (uintptr_t)g) & 15) == 0;
+    p.use_bulk = (aligned && !t.no_bulk) ? 1 : 0;
+    *out = p;
+    return 0;
+}
+
+int check_common(const void* X, const void* S, int noise, int64_t N, int D, int K, const void* la, const void* mu,
+                 const void* Sg) {
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (K < 1 || K > DGMM_MAX_K) return DGMM_ERR_UNSUPPORTED_K;
+    if (noise < 0 || noise > 3) return DGMM_ERR_LAYOUT;
+    if (N < 0 || !la || !mu || !Sg) return DGMM_ERR_BAD_ARG;
+    if (N > 0 && !X) return DGMM_ERR_BAD_ARG;
+    if (N > 0 && noise != NOISE_NONE && !S) return DGMM_ERR_BAD_ARG;
+    return 0;
+}
+
+// Runs prepare + pair kernel; leaves partials in the workspace.  Returns the plan.
+int run_pair(int mode, const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+             const float* mu, const float* Sigma, const float* g, float resp_floor, float* out_ll, void* workspace,
+             size_t workspace_bytes, cudaStream_t st, Plan* plan_out, Workspace* ws_out) {
+    DeviceInfo dev;
+    int rc = device_info(&dev);
+    if (rc) return rc;
+    if (!workspace) return DGMM_ERR_WORKSPACE;
+    Workspace ws = carve(workspace, D, K, dev.sms);
+    if (ws.bytes > workspace_bytes) return DGMM_ERR_WORKSPACE;
+    Plan plan;
+    rc = make_plan(dev, mode, D, K, N, noise, g != nullptr, X, S, g, &plan);
+    if (rc) return rc;
+
+    const int GS = plan.GS;
+    prepare_kernel<<<8, 256, 0, st>>>(log_alpha, mu, Sigma, noise == NOISE_SHARED ? S : nullptr, D, K, GS,
+                                      ws.sig_cols, ws.mu_cols, ws.cj, ws.nonpd);
+    CUDA_TRY(cudaGetLastError());
+
+    PairParams p;
+    p.X = X; p.S = S; p.g = g;
+    p.sig_cols = ws.sig_cols; p.mu_cols = ws.mu_cols; p.cj = ws.cj;
+    p.out_ll = out_ll; p.part = ws.part; p.part_ll = ws.part_ll; p.nonpd = ws.nonpd;
+    p.N = N; p.n_tiles = plan.n_tiles;
+    p.K = K; p.GS = GS; p.NSLOT = plan.NSLOT; p.PT = plan.PT; p.NST = plan.NST; p.noise = noise;
+    p.use_bulk = plan.use_bulk;
+    p.resp_floor = resp_floor;
+    void* args[] = {&p};
+    CUDA_TRY(cudaLaunchKernel(plan.kernel, dim3(plan.grid), dim3(plan.TPB), args, plan.smem, st));
+    *plan_out = plan;
+    *ws_out = ws;
+    return 0;
+}
+
+}  // namespace
+
+// =======================================================================================
+// C ABI
+// =======================================================================================
+extern "C" {
+
+int dgmm_abi_version(void) { return DGMM_ABI_VERSION; }
+
+int dgmm_supported_dims(int* list, int* n) {
+    if (!n) return DGMM_ERR_BAD_ARG;
+    if (list)
+        for (int d = 1; d <= DGMM_MAX_D; ++d) list[d - 1] = d;
+    *n = DGMM_MAX_D;
+    return 0;
+}
+
+size_t dgmm_workspace_bytes(int D, int K) {
+    if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return 0;
+    DeviceInfo dev;
+    if (device_info(&dev)) return 0;
+    return carve(nullptr, D, K, dev.sms).bytes;
+}
+
+// Diagnostics / tuning hook (not part of the drop-in surface): -1 = automatic.
+int dgmm_debug_set_tuning(int sigp, int accp, int nslot, int pt, int nst, int blocks_per_sm, int rc, int no_bulk) {
+    g_tuning.sigp = sigp; g_tuning.accp = accp; g_tuning.nslot = nslot; g_tuning.pt = pt;
+    g_tuning.nst = nst; g_tuning.blocks_per_sm = blocks_per_sm; g_tuning.rc = rc; g_tuning.no_bulk = no_bulk;
+    return 0;
+}
+
+// Diagnostics: the launch plan the library would use (for bench.py / DESIGN.md reporting).
+// out[0..9] = sigp, accp, rc, GS, NSLOT, TPB, PT, NST, grid, smem bytes ; out[10] = use_bulk
+int dgmm_debug_get_plan(int mode, int D, int K, int64_t N, int noise, int has_g, int* out) {
+    DeviceInfo dev;
+    int rc = device_info(&dev);
+    if (rc) return rc;
+    Plan p;
+    rc = make_plan(dev, mode, D, K, N, noise, has_g != 0, nullptr, nullptr, nullptr, &p);
+    if (rc) return rc;
+    out[0] = p.sigp; out[1] = p.accp; out[2] = p.rc; out[3] = p.GS; out[4] = p.NSLOT; out[5] = p.TPB;
+    out[6] = p.PT; out[7] = p.NST; out[8] = p.grid; out[9] = (int)p.smem; out[10] = p.use_bulk;
+    return 0;
+}
+
+int dgmm_loglik_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                    const float* log_alpha, const float* mu, const float* Sigma, float* out_ll, double* out_sum,
+                    int* status, void* workspace, size_t workspace_bytes, void* stream) {
+    int rc = check_common(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    Plan plan;
+    Workspace ws;
+    rc = run_pair(MODE_LOGLIK, X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, nullptr, 0.f, out_ll, workspace,
+                  workspace_bytes, st, &plan, &ws);
+    if (rc) return rc;
+    if (out_sum || status) {
+        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, plan.grid, out_sum, status, 0);
+        CUDA_TRY(cudaGetLastError());
+    }
+    return 0;
+}
+
+int dgmm_estep_stats_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                         const float* log_alpha, const float* mu, const float* Sigma, const float* g,
+                         float resp_floor, float* out_ll, float* out_stats, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+    int rc = check_common(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma);
+    if (rc) return rc;
+    if (!out_stats) return DGMM_ERR_BAD_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    Plan plan;
+    Workspace ws;
+    rc = run_pair(MODE_STATS, X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, g, resp_floor, out_ll, workspace,
+                  workspace_bytes, st, &plan, &ws);
+    if (rc) return rc;
+    const int total = K * (1 + D + D * D) + 1;
+    finalize_stats_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
+                                                               plan.GS, plan.accp == ST_GLOBAL ? plan.TPB : plan.GS,
+                                                               plan.accp == ST_GLOBAL ? plan.NSLOT : 1, out_stats, 0);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int dgmm_estep_full_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                        const float* log_alpha, const float* mu, const float* Sigma, float* out_log_r, float* out_b,
+                        float* out_B, float* out_ll, int* status, void* workspace, size_t workspace_bytes,
+                        void* stream) {
+    int rc = check_common(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma);
+    if (rc) return rc;
+    if (!out_ll) return DGMM_ERR_BAD_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    Plan plan;
+    Workspace ws;
+    rc = run_pair(MODE_LOGLIK, X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, nullptr, 0.f, out_ll, workspace,
+                  workspace_bytes, st, &plan, &ws);
+    if (rc) return rc;
+    if (N > 0 && (out_log_r || out_b || out_B)) {
+        FullParams f;
+        f.X = X; f.S = S; f.log_alpha = log_alpha; f.mu = mu; f.Sigma = Sigma; f.ll = out_ll;
+        f.out_log_r = out_log_r; f.out_b = out_b; f.out_B = out_B; f.nonpd = ws.nonpd;
+        f.N = N; f.K = K; f.noise = noise_layout;
+        const void* k = kDims[D].full();
+        const long long pairs = (long long)N * K;
+        const long long blocks = (pairs + 127) / 128;
+        if (blocks > 0x7fffffffLL) return DGMM_ERR_BAD_ARG;
+        void* args[] = {&f};
+        CUDA_TRY(cudaLaunchKernel(k, dim3((unsigned)blocks), dim3(128), args, 0, st));
+    }
+    if (status) {
+        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, plan.grid, nullptr, status, 0);
+        CUDA_TRY(cudaGetLastError());
+    }
+    return 0;
+}
+
+int dgmm_mstep_update_f32(const float* stats, double n_total, float w, int D, int K, float* mu, float* Sigma,
+                          float* alpha, float* log_alpha, void* stream) {
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (K < 1) return DGMM_ERR_UNSUPPORTED_K;
+    if (!stats || !mu || !Sigma || !alpha || !log_alpha) return DGMM_ERR_BAD_ARG;
+    const size_t sh = (size_t)(3 * D * D + D) * sizeof(double);
+    mstep_kernel<<<K, D * D, sh, (cudaStream_t)stream>>>(stats, n_total, (double)w, D, K, mu, Sigma, alpha, log_alpha);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int dgmm_fp32_probe(float* sink, int iters, double* flops, void* stream) {
+    DeviceInfo dev;
+    int rc = device_info(&dev);
+    if (rc) return rc;
+    if (!sink || iters < 1) return DGMM_ERR_BAD_ARG;
+    const int blocks = dev.sms * 8, threads = 256;
+    fp32_probe_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(sink, iters);
+    CUDA_TRY(cudaGetLastError());
+    if (flops) *flops = (double)blocks * threads * (double)iters * 16.0 * 8.0 * 2.0;
+    return 0;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// host-buffer pipeline
+// ---------------------------------------------------------------------------------------
+struct dgmm_ctx {
+    int device, D, K;
+    int64_t chunk;
+    cudaStream_t copy_st, comp_st;
+    cudaEvent_t loaded[2], consumed[2];
+    float* dX[2];
+    float* dS[2];
+    float* d_ll[2];
+    float *d_alpha, *d_log_alpha, *d_mu, *d_Sigma, *d_stats;
+    double* d_sum;
+    double* h_sum;   // pinned, 2 doubles
+    float* h_tail;   // pinned, 4 floats
+    void* ws;
+    size_t ws_bytes;
+};
+
+extern "C" {
+
+int dgmm_ctx_create(dgmm_ctx** out, int device, int D, int K, int64_t chunk_points) {
+    if (!out || chunk_points < 1) return DGMM_ERR_BAD_ARG;
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (K < 1 || K > DGMM_MAX_K) return DGMM_ERR_UNSUPPORTED_K;
+    CUDA_TRY(cudaSetDevice(device));
+    dgmm_ctx* c = (dgmm_ctx*)calloc(1, sizeof(dgmm_ctx));
+    if (!c) return DGMM_ERR_BAD_ARG;
+    c->device = device; c->D = D; c->K = K; c->chunk = chunk_points;
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->copy_st, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->comp_st, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        CUDA_TRY(cudaEventCreateWithFlags(&c->loaded[i], cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&c->consumed[i], cudaEventDisableTiming));
+        CUDA_TRY(cudaMalloc(&c->dX[i], (size_t)chunk_points * D * 4));
+        CUDA_TRY(cudaMalloc(&c->dS[i], (size_t)chunk_points * D * D * 4));
+        CUDA_TRY(cudaMalloc(&c->d_ll[i], (size_t)chunk_points * 4));
+    }
+    CUDA_TRY(cudaMalloc(&c->d_alpha, (size_t)K * 4));
+    CUDA_TRY(cudaMalloc(&c->d_log_alpha, (size_t)K * 4));
+    CUDA_TRY(cudaMalloc(&c->d_mu, (size_t)K * D * 4));
+    CUDA_TRY(cudaMalloc(&c->d_Sigma, (size_t)K * D * D * 4));
+    CUDA_TRY(cudaMalloc(&c->d_stats, dgmm_stats_len(D, K) * 4));
+    CUDA_TRY(cudaMalloc(&c->d_sum, 2 * sizeof(double)));
+    CUDA_TRY(cudaMallocHost(&c->h_sum, 2 * sizeof(double)));
+    CUDA_TRY(cudaMallocHost(&c->h_tail, 4 * sizeof(float)));
+    c->ws_bytes = dgmm_workspace_bytes(D, K);
+    if (!c->ws_bytes) return DGMM_ERR_NO_DEVICE;
+    CUDA_TRY(cudaMalloc(&c->ws, c->ws_bytes));
+    *out = c;
+    return 0;
+}
+
+void dgmm_ctx_destroy(dgmm_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (int i = 0; i < 2; ++i) {
+        if (c->dX[i]) cudaFree(c->dX[i]);
+        if (c->dS[i]) cudaFree(c->dS[i]);
+        if (c->d_ll[i]) cudaFree(c->d_ll[i]);
+        if (c->loaded[i]) cudaEventDestroy(c->loaded[i]);
+        if (c->consumed[i]) cudaEventDestroy(c->consumed[i]);
+    }
+    cudaFree(c->d_alpha); cudaFree(c->d_log_alpha); cudaFree(c->d_mu); cudaFree(c->d_Sigma);
+    cudaFree(c->d_stats); cudaFree(c->d_sum); cudaFree(c->ws);
+    cudaFreeHost(c->h_sum); cudaFreeHost(c->h_tail);
+    if (c->copy_st) cudaStreamDestroy(c->copy_st);
+    if (c->comp_st) cudaStreamDestroy(c->comp_st);
+    free(c);
+}
+
+}  // extern "C"
+
+static size_t noise_floats(int D, int layout) {
+    return layout == DGMM_NOISE_FULL ? (size_t)D * D : (layout == DGMM_NOISE_DIAG ? (size_t)D : 0);
+}
+
+// Streams the chunks of (X, S) through the two device buffers: copy stream uploads chunk c+1
+// while the compute stream works on chunk c.  `body(chunk_index, n, dX, dS)` enqueues the
+// kernels of one chunk on the compute stream.
+template <class Body>
+static int stream_chunks(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, Body body) {
+    const int D = c->D;
+    const size_t nf = noise_floats(D, layout);
+    const float* dShared = nullptr;
+    if (layout == DGMM_NOISE_SHARED) {
+        CUDA_TRY(cudaMemcpyAsync(c->dS[0], S, (size_t)D * D * 4, cudaMemcpyHostToDevice, c->comp_st));
+        dShared = c->dS[0];
+    }
+    int64_t done = 0;
+    int idx = 0;
+    while (done < N) {
+        const int64_t n = std::min<int64_t>(c->chunk, N - done);
+        const int b = idx & 1;
+        if (idx >= 2) CUDA_TRY(cudaStreamWaitEvent(c->copy_st, c->consumed[b], 0));
+        CUDA_TRY(cudaMemcpyAsync(c->dX[b], X + (size_t)done * D, (size_t)n * D * 4, cudaMemcpyHostToDevice, c->copy_st));
+        if (nf)
+            CUDA_TRY(cudaMemcpyAsync(c->dS[b], S + (size_t)done * nf, (size_t)n * nf * 4, cudaMemcpyHostToDevice,
+                                     c->copy_st));
+        CUDA_TRY(cudaEventRecord(c->loaded[b], c->copy_st));
+        CUDA_TRY(cudaStreamWaitEvent(c->comp_st, c->loaded[b], 0));
+        int rc = body(idx, done, n, c->dX[b], layout == DGMM_NOISE_SHARED ? dShared : c->dS[b]);
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(c->consumed[b], c->comp_st));
+        done += n;
+        ++idx;
+    }
+    return 0;
+}
+
+extern "C" {
+
+int dgmm_em_iteration_host(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, float w, float* alpha,
+                           float* mu, float* Sigma, double* ll_sum, int64_t* nonpd) {
+    if (!c || !alpha || !mu || !Sigma) return DGMM_ERR_BAD_ARG;
+    if (layout < 0 || layout > 3) return DGMM_ERR_LAYOUT;
+    if (layout == DGMM_NOISE_SHARED && c->chunk < c->D) return DGMM_ERR_BAD_ARG;
+    CUDA_TRY(cudaSetDevice(c->device));
+    const int D = c->D, K = c->K;
+    cudaStream_t st = c->comp_st;
+    CUDA_TRY(cudaMemcpyAsync(c->d_alpha, alpha, (size_t)K * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->d_mu, mu, (size_t)K * D * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->d_Sigma, Sigma, (size_t)K * D * D * 4, cudaMemcpyHostToDevice, st));
+    log_kernel<<<(K + 127) / 128, 128, 0, st>>>(c->d_alpha, c->d_log_alpha, K);
+    CUDA_TRY(cudaMemsetAsync(c->d_stats, 0, dgmm_stats_len(D, K) * 4, st));
+    int rc = stream_chunks(c, X, S, layout, N, [&](int, int64_t, int64_t n, const float* dX, const float* dS) -> int {
+        Plan plan;
+        Workspace ws;
+        int r = run_pair(MODE_STATS, dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr, 0.f,
+                         nullptr, c->ws, c->ws_bytes, st, &plan, &ws);
+        if (r) return r;
+        const int total = K * (1 + D + D * D) + 1;
+        finalize_stats_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
+                                                                   plan.GS, plan.accp == ST_GLOBAL ? plan.TPB : plan.GS,
+                                                                   plan.accp == ST_GLOBAL ? plan.NSLOT : 1, c->d_stats, 1);
+        return (int)cudaGetLastError();
+    });
+    if (rc) return rc;
+    rc = dgmm_mstep_update_f32(c->d_stats, (double)N, w, D, K, c->d_mu, c->d_Sigma, c->d_alpha, c->d_log_alpha, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(alpha, c->d_alpha, (size_t)K * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(mu, c->d_mu, (size_t)K * D * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(Sigma, c->d_Sigma, (size_t)K * D * D * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_tail, c->d_stats + (size_t)K * (1 + D + D * D), 4 * sizeof(float),
+                             cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (ll_sum) *ll_sum = (double)c->h_tail[0] + (double)c->h_tail[1];
+    if (nonpd) *nonpd = (int64_t)c->h_tail[3];
+    if (c->h_tail[3] > 0.f && ll_sum) *ll_sum = -INFINITY;
+    return 0;
+}
+
+int dgmm_score_host(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, const float* alpha,
+                    const float* mu, const float* Sigma, float* out_ll, double* ll_sum, int64_t* nonpd) {
+    if (!c || !alpha || !mu || !Sigma) return DGMM_ERR_BAD_ARG;
+    if (layout < 0 || layout > 3) return DGMM_ERR_LAYOUT;
+    CUDA_TRY(cudaSetDevice(c->device));
+    const int D = c->D, K = c->K;
+    cudaStream_t st = c->comp_st;
+    CUDA_TRY(cudaMemcpyAsync(c->d_alpha, alpha, (size_t)K * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->d_mu, mu, (size_t)K * D * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->d_Sigma, Sigma, (size_t)K * D * D * 4, cudaMemcpyHostToDevice, st));
+    log_kernel<<<(K + 127) / 128, 128, 0, st>>>(c->d_alpha, c->d_log_alpha, K);
+    CUDA_TRY(cudaMemsetAsync(c->d_sum, 0, 2 * sizeof(double), st));
+    int rc = stream_chunks(c, X, S, layout, N, [&](int idx, int64_t off, int64_t n, const float* dX, const float* dS) -> int {
+        float* dll = c->d_ll[idx & 1];  // safe to reuse: its D2H copy two chunks ago is ordered on `st`
+        Plan plan;
+        Workspace ws;
+        int r = run_pair(MODE_LOGLIK, dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr, 0.f, dll,
+                         c->ws, c->ws_bytes, st, &plan, &ws);
+        if (r) return r;
+        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, plan.grid, c->d_sum, nullptr, 1);
+        CUDA_TRY(cudaGetLastError());
+        if (out_ll) CUDA_TRY(cudaMemcpyAsync(out_ll + off, dll, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        return 0;
+    });
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(c->h_sum, c->d_sum, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const double total = c->h_sum[0];
+    const int64_t bad = (int64_t)c->h_sum[1];
+    if (ll_sum) *ll_sum = bad ? -INFINITY : total;
+    if (nonpd) *nonpd = bad;
+    return 0;
+}
+
+}  // extern "C"

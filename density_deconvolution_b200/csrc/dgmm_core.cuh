@@ -1,0 +1,115 @@
+// dgmm_core.cuh -- per-(point, component) small-D linear algebra, thread-private.
+//
+// One thread owns one pair (i, j) and keeps the packed lower triangle of
+// T_ij = Sigma_j + S_i in registers (D <= DGMM_UNROLL_D: every loop fully unrolled so that
+// all indices are static) or in local memory (larger D: rolled loops, slower, same maths).
+//
+// What the reference does with batched LAPACK calls on materialised [N,K,D,D] tensors
+// (deconv/gmm/deconv_gmm.py:43-62: cholesky, cholesky_solve(I), matmuls) is done here in
+// place on D(D+1)/2 floats:
+//   chol_forward : T = L L^T (right-looking), y = L^{-1} d carried as an extra row,
+//                  sum log2 of the pivots; the diagonal is left holding 1/L_kk.
+//   tri_inverse  : L -> L^{-1} in place.
+//   back_apply   : u = L^{-T} y = T^{-1} d.
+//   gram_lower   : L^{-1} -> T^{-1} = L^{-T} L^{-1} (lower triangle) in place.
+//
+// The functions are __host__ __device__ so that tests/ can compile them for the CPU and
+// check the index arithmetic against the oracle without a GPU (test tool only; the
+// product has no CPU path).
+#pragma once
+
+#include <math.h>
+#include <float.h>
+
+#if defined(__CUDACC__)
+#define DGMM_HD __host__ __device__ __forceinline__
+#else
+#define DGMM_HD inline
+#endif
+
+#ifndef DGMM_UNROLL_D
+#define DGMM_UNROLL_D 16
+#endif
+
+namespace dgmm {
+
+DGMM_HD constexpr int tri(int a, int b) { return a * (a + 1) / 2 + b; }  // requires b <= a
+// row of packed-triangle position t (inverse of tri); folds to a constant for constant t
+DGMM_HD constexpr int tri_row(int t) {
+    int a = 0;
+    while ((a + 1) * (a + 2) / 2 <= t) ++a;
+    return a;
+}
+// per-thread column stride: a multiple of 4 floats holding an odd number of float4s, so that
+// 32 threads reading their own column with 128-bit accesses never conflict on a bank
+DGMM_HD constexpr int pad_col(int n) {
+    int m = (n + 3) / 4;
+    if (m % 2 == 0) ++m;
+    return 4 * m;
+}
+
+template <int D>
+struct Dim {
+    static constexpr int ND = D * (D + 1) / 2;  // packed lower triangle
+    static constexpr int NS = 1 + D + ND;       // per-component packed statistics s0|s1|S2(lower)
+};
+
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kHalfLog2Pi = 0.9189385332046727f;
+
+DGMM_HD float mufu_rsqrt(float x) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#else
+    return 1.0f / sqrtf(x);
+#endif
+}
+
+DGMM_HD float mufu_lg2(float x) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#else
+    return log2f(x);
+#endif
+}
+
+DGMM_HD float mufu_ex2(float x) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#else
+    return exp2f(x);
+#endif
+}
+
+// 1/sqrt(p): MUFU.RSQ plus one Newton step (full fp32 accuracy; pivots may span
+// 1e-4 .. 1e12, SURVEY.md 7.2 "dynamic range of S_i").
+DGMM_HD float rsqrt_refined(float p) {
+    float r = mufu_rsqrt(p);
+    float h = 0.5f * p * r;
+    return fmaf(r, fmaf(-h, r, 0.5f), r);
+}
+
+}  // namespace dgmm
+
+#define DGMM_LOOP _Pragma("unroll")
+namespace dgmm {
+namespace unrolled {
+#include "dgmm_core_body.inc"
+}  // namespace unrolled
+}  // namespace dgmm
+#undef DGMM_LOOP
+
+#define DGMM_LOOP _Pragma("unroll 1")
+namespace dgmm {
+namespace rolled {
+#include "dgmm_core_body.inc"
+}  // namespace rolled
+}  // namespace dgmm
+#undef DGMM_LOOP

@@ -1,0 +1,48 @@
+// dgmm_full.cuh -- materialising E-step (small N): log r [N,K], b [N,K,D], B [N,K,D,D].
+//
+// One thread per (point, component) pair, flat over N*K.  Replaces the posterior-moment
+// part of DeconvGMM._e_step (deconv/gmm/deconv_gmm.py:64-79) and
+// SGDDeconvGMM.posterior_params (deconv/gmm/sgd_deconv_gmm.py:71-94):
+//   b_ij = mu_j + Sigma_j u_ij,   B_ij = Sigma_j - Sigma_j T_ij^{-1} Sigma_j.
+// ll_i comes from a preceding log-likelihood pass (pair kernel), so log r = log p - ll.
+// The output is N*K*D*D floats: this kernel is bound by its own HBM writes and is meant
+// for the API-parity call sites, not for the N = 1e7 path (256 GB at c2).
+#pragma once
+
+#include "dgmm_core.cuh"
+#include "dgmm_pair.cuh"
+
+namespace dgmm {
+
+struct FullParams {
+    const float* X;
+    const float* S;
+    const float* log_alpha;  // [K]
+    const float* mu;         // [K,D]
+    const float* Sigma;      // [K,D,D]
+    const float* ll;         // [N]
+    float* out_log_r;        // [N,K] or null
+    float* out_b;            // [N,K,D] or null
+    float* out_B;            // [N,K,D,D] or null
+    int* nonpd;
+    long long N;
+    int K, noise;
+};
+
+}  // namespace dgmm
+
+#define DGMM_LOOP _Pragma("unroll")
+namespace dgmm {
+namespace unrolled {
+#include "dgmm_full_body.inc"
+}  // namespace unrolled
+}  // namespace dgmm
+#undef DGMM_LOOP
+
+#define DGMM_LOOP _Pragma("unroll 1")
+namespace dgmm {
+namespace rolled {
+#include "dgmm_full_body.inc"
+}  // namespace rolled
+}  // namespace dgmm
+#undef DGMM_LOOP

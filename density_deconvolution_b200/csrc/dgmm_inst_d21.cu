@@ -1,0 +1,3 @@
+// Instantiates the pair / full kernels for D = 21 (see dgmm_tables.cuh).
+#include "dgmm_tables.cuh"
+DGMM_DEFINE_DIM(21)

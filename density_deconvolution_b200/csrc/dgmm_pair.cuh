@@ -1,0 +1,138 @@
+// dgmm_pair.cuh -- the fused log-likelihood / E-step-statistics kernel for sm_100a.
+//
+// Mapping ("threads are components"): a group of GS threads owns one data point at a time;
+// thread `jl` of the group owns mixture component j = jl for the whole kernel.  A block
+// holds NSLOT such groups.  For the point in its slot every thread
+//   1. forms T = Sigma_j + S_i (Sigma_j: its private column in shared memory or global;
+//      S_i: broadcast reads from the TMA-staged tile),
+//   2. factorises T in registers (dgmm_core.cuh) and gets log p_ij,
+//   3. takes part in the logsumexp over the group (warp shuffles; for GS > 32 one shared
+//      exchange + a named barrier per point) -> ll_i, r_ij,
+//   4. (MODE_STATS) inverts the factor and adds omega_ij * {1, u, u u^T - T^{-1}} to its
+//      PRIVATE accumulators (registers / shared columns / global columns).
+// Because component j never leaves the thread there is no cross-lane reduction of the
+// K(1+D+D(D+1)/2) statistics in the hot loop, and because the group covers all K components
+// at once, ll_i is known before the statistics are weighted: one pass, no recomputation
+// (SURVEY.md 7.2 "two normalisations").
+//
+// Input streaming: the points of a tile are contiguous in X [N,D] and S [N,D,D], so one
+// tile is three 1-D bulk copies (cp.async.bulk -> UBLKCP, the TMA engine) into a NST-deep
+// shared-memory ring signalled through mbarriers; unaligned bases and the ragged last tile
+// take a cooperative LDG->STS path in the same kernel.
+//
+// Replaces deconv/gmm/deconv_gmm.py:39-107 and deconv/gmm/sgd_deconv_gmm.py:14-28 of the
+// reference (see include/dgmm_b200.h for the per-entry-point map).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dgmm_core.cuh"
+
+namespace dgmm {
+
+enum : int { MODE_LOGLIK = 0, MODE_STATS = 1 };
+enum : int { ST_REG = 0, ST_SMEM = 1, ST_GLOBAL = 2 };  // where Sigma_j / accumulators live
+enum : int { NOISE_FULL = 0, NOISE_DIAG = 1, NOISE_NONE = 2, NOISE_SHARED = 3 };
+
+constexpr int kMaxStages = 4;
+constexpr int kPairMaxThreads = 256;  // largest block the pair kernel is compiled for
+constexpr int kSmemHeader = 1152;  // mbarriers (64 B) + logsumexp exchange (512 B) + double reduce (512 B)
+
+struct PairParams {
+    const float* X;          // [N,D]
+    const float* S;          // [N,D,D] | [N,D] | unused
+    const float* g;          // [N] or null
+    const float* sig_cols;   // [ND][GS]  transposed packed lower triangles (+ shared noise folded in)
+    const float* mu_cols;    // [D][GS]
+    const float* cj;         // [GS]  log alpha_j - D/2 log 2pi  (-inf for j >= K)
+    float* out_ll;           // [N] or null
+    float* part;             // [grid][NS][GS]  per-block partial statistics
+    double* part_ll;         // [grid][2]       per-block sum ll, sum g
+    int* nonpd;              // [1] device counter
+    long long N;
+    long long n_tiles;
+    int K, GS, NSLOT, PT, NST, noise;
+    int use_bulk;
+    float resp_floor;
+};
+
+// ---------------------------------------------------------------------------------------
+// PTX helpers (mbarrier + 1-D bulk copy)
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return done != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Bytes of one ring stage and the offsets of its three sub-tiles (all multiples of 16).
+__host__ __device__ inline int noise_floats_per_point(int D, int noise) {
+    return noise == NOISE_FULL ? D * D : (noise == NOISE_DIAG ? D : 0);
+}
+__host__ __device__ inline int align16(int b) { return (b + 15) & ~15; }
+struct StageLayout {
+    int off_S, off_X, off_g, bytes;
+};
+__host__ __device__ inline StageLayout stage_layout(int D, int noise, int PT, bool has_g) {
+    StageLayout L;
+    L.off_S = 0;
+    L.off_X = align16(PT * noise_floats_per_point(D, noise) * 4);
+    L.off_g = L.off_X + align16(PT * D * 4);
+    L.bytes = L.off_g + (has_g ? align16(PT * 4) : 0);
+    L.bytes = (L.bytes + 127) & ~127;
+    return L;
+}
+
+}  // namespace dgmm
+
+#define DGMM_LOOP _Pragma("unroll")
+namespace dgmm {
+namespace unrolled {
+#include "dgmm_pair_body.inc"
+}  // namespace unrolled
+}  // namespace dgmm
+#undef DGMM_LOOP
+
+#define DGMM_LOOP _Pragma("unroll 1")
+namespace dgmm {
+namespace rolled {
+#include "dgmm_pair_body.inc"
+}  // namespace rolled
+}  // namespace dgmm
+#undef DGMM_LOOP

@@ -1,0 +1,44 @@
+"""Cross-GPU exchange of the hot path: ONE all-reduce(SUM) of the packed statistics buffer per
+EM iteration / SGD step.  One process per GPU; points are sharded contiguously
+by rank; parameters are replicated and every rank applies the identical update, so no
+broadcast is needed.  ``torch.distributed`` (NCCL on GPUs, gloo in the CPU tests) is the
+plumbing."""
+import torch
+import torch.distributed as dist
+
+
+def is_distributed():
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+
+def world_size():
+    return dist.get_world_size() if is_distributed() else 1
+
+
+def rank():
+    return dist.get_rank() if is_distributed() else 0
+
+
+def shard_bounds(n, r=None, ws=None):
+    """Contiguous ``[lo, hi)`` slice of ``n`` points owned by rank ``r``."""
+    r = rank() if r is None else r
+    ws = world_size() if ws is None else ws
+    base, rem = divmod(n, ws)
+    lo = r * base + min(r, rem)
+    return lo, lo + base + (1 if r < rem else 0)
+
+
+def allreduce_stats(stats):
+    """In-place SUM of the packed statistics across ranks (no-op for one process).
+    Every slot of the buffer is additive, including the (ll_hi, ll_lo) float pair."""
+    if is_distributed():
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    return stats
+
+
+def allreduce_scalar_sum(value, device):
+    if not is_distributed():
+        return value
+    t = torch.tensor([value], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t.item()

@@ -1,0 +1,193 @@
+"""Tensor-level wrappers around the C ABI (device pointers of torch CUDA tensors in,
+launches on torch's current stream).  torch is plumbing here: memory, streams."""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import NOISE_LAYOUTS, DgmmError, check
+
+_workspaces = {}
+
+
+def stats_len(D, K):
+    return K * (1 + D + D * D) + 4
+
+
+def _f32c(t, name, device=None):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError("%s must be a torch.Tensor" % name)
+    if not t.is_cuda:
+        raise DgmmError("%s must live on a CUDA device (the B200 path has no CPU fallback)" % name)
+    if t.dtype != torch.float32:
+        raise TypeError("%s must be float32, got %s" % (name, t.dtype))
+    if device is not None and t.device != device:
+        raise DgmmError("%s is on %s, expected %s" % (name, t.device, device))
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _stream(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def workspace(D, K, device):
+    key = (D, K, device.index if device.index is not None else torch.cuda.current_device())
+    ws = _workspaces.get(key)
+    if ws is None:
+        with torch.cuda.device(device):
+            nbytes = _lib.lib().dgmm_workspace_bytes(D, K)
+        if nbytes == 0:
+            raise DgmmError("dgmm_workspace_bytes(D=%d, K=%d) failed (unsupported shape or no sm_100 device)" % (D, K))
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def _noise(S, layout, N, D, device):
+    code = NOISE_LAYOUTS[layout] if isinstance(layout, str) else int(layout)
+    if code == _lib.NOISE_NONE:
+        return None, code
+    S = _f32c(S, "noise_covars", device)
+    want = {_lib.NOISE_FULL: (N, D, D), _lib.NOISE_DIAG: (N, D), _lib.NOISE_SHARED: (D, D)}[code]
+    if tuple(S.shape) != want:
+        raise ValueError("noise_covars has shape %s, expected %s for layout %r" % (tuple(S.shape), want, layout))
+    return S, code
+
+
+def _params(log_alpha, mu, Sigma, device):
+    mu = _f32c(mu, "means", device)
+    K, D = mu.shape
+    Sigma = _f32c(Sigma, "covars", device)
+    log_alpha = _f32c(log_alpha, "log_alpha", device).reshape(-1)
+    if tuple(Sigma.shape) != (K, D, D) or log_alpha.numel() != K:
+        raise ValueError("parameter shapes disagree: means %s covars %s log_alpha %s"
+                         % (tuple(mu.shape), tuple(Sigma.shape), tuple(log_alpha.shape)))
+    return log_alpha, mu, Sigma, K, D
+
+
+def loglik(X, S, log_alpha, mu, Sigma, noise="full", want_sum=False):
+    """``ll_i = log sum_j alpha_j N(x_i | mu_j, Sigma_j + S_i)`` -> ``[N]`` float32.
+    With ``want_sum`` also returns a float64 device tensor ``[sum_i ll_i, n_nonpd]``."""
+    X = _f32c(X, "X")
+    dev = X.device
+    N, D = X.shape
+    log_alpha, mu, Sigma, K, D2 = _params(log_alpha, mu, Sigma, dev)
+    if D2 != D:
+        raise ValueError("X has D=%d but means have D=%d" % (D, D2))
+    S, code = _noise(S, noise, N, D, dev)
+    ll = torch.empty(N, dtype=torch.float32, device=dev)
+    sums = torch.empty(2, dtype=torch.float64, device=dev)
+    ws = workspace(D, K, dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_loglik_f32(_ptr(X), _ptr(S), code, N, D, K, _ptr(log_alpha), _ptr(mu), _ptr(Sigma),
+                                        _ptr(ll), _ptr(sums), None, _ptr(ws), ws.numel(), _stream(dev))
+    check(rc, "dgmm_loglik_f32")
+    return (ll, sums) if want_sum else ll
+
+
+def estep_stats(X, S, log_alpha, mu, Sigma, g=None, resp_floor=0.0, noise="full", want_ll=True, out_stats=None):
+    """Fused E-step + sufficient statistics.  Returns ``(ll [N] or None, stats)`` with
+    ``stats`` the packed float32 buffer of ``include/dgmm_b200.h``."""
+    X = _f32c(X, "X")
+    dev = X.device
+    N, D = X.shape
+    log_alpha, mu, Sigma, K, D2 = _params(log_alpha, mu, Sigma, dev)
+    if D2 != D:
+        raise ValueError("X has D=%d but means have D=%d" % (D, D2))
+    S, code = _noise(S, noise, N, D, dev)
+    if g is not None:
+        g = _f32c(g, "g", dev).reshape(-1)
+        if g.numel() != N:
+            raise ValueError("g must have N elements")
+    ll = torch.empty(N, dtype=torch.float32, device=dev) if want_ll else None
+    if out_stats is None:
+        out_stats = torch.empty(stats_len(D, K), dtype=torch.float32, device=dev)
+    ws = workspace(D, K, dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_estep_stats_f32(_ptr(X), _ptr(S), code, N, D, K, _ptr(log_alpha), _ptr(mu), _ptr(Sigma),
+                                             _ptr(g), float(resp_floor), _ptr(ll), _ptr(out_stats), _ptr(ws),
+                                             ws.numel(), _stream(dev))
+    check(rc, "dgmm_estep_stats_f32")
+    return ll, out_stats
+
+
+def estep_full(X, S, log_alpha, mu, Sigma, noise="full", want_means=True, want_covars=True):
+    """Materialising E-step: ``(ll [N], log_r [N,K], b [N,K,D], B [N,K,D,D], status)``."""
+    X = _f32c(X, "X")
+    dev = X.device
+    N, D = X.shape
+    log_alpha, mu, Sigma, K, D2 = _params(log_alpha, mu, Sigma, dev)
+    if D2 != D:
+        raise ValueError("X has D=%d but means have D=%d" % (D, D2))
+    S, code = _noise(S, noise, N, D, dev)
+    ll = torch.empty(N, dtype=torch.float32, device=dev)
+    log_r = torch.empty(N, K, dtype=torch.float32, device=dev)
+    b = torch.empty(N, K, D, dtype=torch.float32, device=dev) if want_means else None
+    B = torch.empty(N, K, D, D, dtype=torch.float32, device=dev) if want_covars else None
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws = workspace(D, K, dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_estep_full_f32(_ptr(X), _ptr(S), code, N, D, K, _ptr(log_alpha), _ptr(mu), _ptr(Sigma),
+                                            _ptr(log_r), _ptr(b), _ptr(B), _ptr(ll), _ptr(status), _ptr(ws),
+                                            ws.numel(), _stream(dev))
+    check(rc, "dgmm_estep_full_f32")
+    return ll, log_r, b, B, status
+
+
+def mstep_update(stats, n_total, w, mu, Sigma, alpha, log_alpha):
+    """In-place closed-form EM update of ``mu, Sigma, alpha, log_alpha`` from packed stats."""
+    dev = stats.device
+    K, D = mu.shape
+    for name, t in (("stats", stats), ("means", mu), ("covars", Sigma), ("alpha", alpha), ("log_alpha", log_alpha)):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise DgmmError("%s must be a contiguous float32 CUDA tensor (updated in place)" % name)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_mstep_update_f32(_ptr(stats), float(n_total), float(w), D, K, _ptr(mu), _ptr(Sigma),
+                                              _ptr(alpha), _ptr(log_alpha), _stream(dev))
+    check(rc, "dgmm_mstep_update_f32")
+
+
+def unpack_stats(stats, D, K):
+    """Views into the packed buffer: ``s0 [K], s1 [K,D], S2 [K,D,D], tail [4]``
+    (tail = ll_hi, ll_lo, sum_g, nonpd)."""
+    o = 0
+    s0 = stats[o:o + K]; o += K
+    s1 = stats[o:o + K * D].view(K, D); o += K * D
+    S2 = stats[o:o + K * D * D].view(K, D, D); o += K * D * D
+    return s0, s1, S2, stats[o:o + 4]
+
+
+def set_tuning(sigp=-1, accp=-1, nslot=-1, pt=-1, nst=-1, blocks_per_sm=-1, rc=-1, no_bulk=0):
+    check(_lib.lib().dgmm_debug_set_tuning(sigp, accp, nslot, pt, nst, blocks_per_sm, rc, no_bulk), "set_tuning")
+
+
+def get_plan(mode, D, K, N, noise="full", has_g=False):
+    out = (ctypes.c_int * 11)()
+    code = NOISE_LAYOUTS[noise] if isinstance(noise, str) else int(noise)
+    check(_lib.lib().dgmm_debug_get_plan(mode, D, K, N, code, int(has_g), out), "get_plan")
+    keys = ("sigp", "accp", "rc", "GS", "NSLOT", "TPB", "PT", "NST", "grid", "smem", "use_bulk")
+    return dict(zip(keys, list(out)))
+
+
+def fp32_probe(device, iters=4096, reps=5):
+    """Measured FP32-FMA throughput (FLOP/s) of a register-only FFMA chain on ``device``."""
+    sink = torch.zeros(1, dtype=torch.float32, device=device)
+    flops = ctypes.c_double(0.0)
+    best = 0.0
+    with torch.cuda.device(device):
+        st = _stream(device)
+        check(_lib.lib().dgmm_fp32_probe(_ptr(sink), iters, ctypes.byref(flops), st), "fp32_probe")
+        torch.cuda.synchronize(device)
+        for _ in range(reps):
+            a = torch.cuda.Event(enable_timing=True)
+            b = torch.cuda.Event(enable_timing=True)
+            a.record()
+            check(_lib.lib().dgmm_fp32_probe(_ptr(sink), iters, ctypes.byref(flops), st), "fp32_probe")
+            b.record()
+            torch.cuda.synchronize(device)
+            best = max(best, flops.value / (a.elapsed_time(b) * 1e-3))
+    return best

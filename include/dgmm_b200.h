@@ -1,0 +1,171 @@
+/*
+ * dgmm_b200.h -- C ABI of the B200-native deconvolution-GMM hot path.
+ *
+ * This is the drop-in boundary.  The reference (bayesiains/density-deconvolution) has no
+ * FFI layer of its own: its hot path is ~70 lines of batched torch ops inside the Python
+ * classes of deconv/gmm/.  Each entry point below names the reference lines it replaces
+ * (paths relative to the reference checkout).  The Python shim that keeps the reference's
+ * class API on top of these calls lives in density_deconvolution_b200/ and the ctypes
+ * binding a maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain C: pointers, sizes, a stream handle; no torch types.
+ *   - all float32, row-major, exactly the reference's tensor layouts:
+ *       X [N,D], noise S [N,D,D], means [K,D], covars [K,D,D].
+ *   - "device" entry points take caller-owned DEVICE pointers, never allocate, and are
+ *     asynchronous on `stream` (a cudaStream_t passed as void*; NULL = default stream).
+ *     Workspace is caller-provided; query its size with dgmm_workspace_bytes().
+ *   - "host" entry points (suffix _host) take HOST pointers, stage through device memory
+ *     they own inside an opaque dgmm_ctx, and return after the result is on the host.
+ *   - return value: 0 = ok, <0 = argument / capability error (see DGMM_ERR_*), >0 = CUDA
+ *     error code from the runtime (cudaError_t).  Numerical failure (some Sigma_j + S_i not
+ *     positive definite) is NOT a return code: it is counted in `status[0]` (device int) or
+ *     in the `nonpd` slot of the packed statistics, and the affected ll_i are -inf, which
+ *     is how the reference reports it (deconv/gmm/deconv_gmm.py:44-47 returns -inf).
+ *   - there is no CPU fallback anywhere in this library.
+ */
+#ifndef DGMM_B200_H
+#define DGMM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define DGMM_API __attribute__((visibility("default")))
+#else
+#define DGMM_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DGMM_ABI_VERSION 1
+#define DGMM_MAX_D 32
+#define DGMM_MAX_K 256
+
+/* error codes (negative) */
+#define DGMM_OK 0
+#define DGMM_ERR_BAD_ARG (-1)        /* null pointer, N<0, K<1 ...                      */
+#define DGMM_ERR_UNSUPPORTED_D (-2)  /* D outside 1..DGMM_MAX_D                         */
+#define DGMM_ERR_UNSUPPORTED_K (-3)  /* K outside 1..DGMM_MAX_K                         */
+#define DGMM_ERR_WORKSPACE (-4)      /* workspace too small / null                      */
+#define DGMM_ERR_LAYOUT (-5)         /* unknown noise layout                            */
+#define DGMM_ERR_NO_DEVICE (-6)      /* no CUDA device / not an sm_100 part             */
+
+/* noise-covariance layouts (the reference contract is DGMM_NOISE_FULL:
+ * deconv/gmm/data.py:7-17, deconv/gmm/sgd_deconv_gmm.py:31-41) */
+#define DGMM_NOISE_FULL 0   /* S [N,D,D]; only the lower triangle is read (potrf 'L') */
+#define DGMM_NOISE_DIAG 1   /* S [N,D]   = diagonal of each S_i                          */
+#define DGMM_NOISE_NONE 2   /* S ignored (S_i = 0): SGDGMMModule.forward, sgd_gmm.py:49-62 */
+#define DGMM_NOISE_SHARED 3 /* S [D,D]   one matrix for all points (data_gen.py:50-53)   */
+
+/* Packed statistics buffer written by dgmm_estep_stats_f32.
+ *   [ s0 (K) | s1 (K*D) | S2 (K*D*D, full symmetric) | ll_hi | ll_lo | sum_g | nonpd ]
+ * with omega_ij = g_i (r_ij + resp_floor), u_ij = T_ij^{-1}(x_i - mu_j):
+ *   s0_j = sum_i omega_ij, s1_j = sum_i omega_ij u_ij, S2_j = sum_i omega_ij (u u^T - T^{-1}),
+ *   ll_hi + ll_lo = sum_i ll_i (a float pair carrying a double through a float32
+ *   all-reduce), sum_g = sum_i g_i, nonpd = number of non-PD (point,component) pairs.
+ * Every slot is additive across shards: one all-reduce(SUM) of this buffer is the whole
+ * cross-GPU exchange of an EM iteration or SGD step. */
+static inline size_t dgmm_stats_len(int D, int K) {
+    return (size_t)K * (size_t)(1 + D + D * D) + 4;
+}
+
+/* ---- capability / sizing ------------------------------------------------------------ */
+
+DGMM_API int dgmm_abi_version(void);
+
+/* Fills list[0..*n) with the supported dimensions (1..DGMM_MAX_D); list may be NULL. */
+DGMM_API int dgmm_supported_dims(int* list, int* n);
+
+/* Bytes of device workspace needed by dgmm_loglik_f32 / dgmm_estep_stats_f32 /
+ * dgmm_estep_full_f32 for this shape on the current device (0 on error). */
+DGMM_API size_t dgmm_workspace_bytes(int D, int K);
+
+/* ---- device entry points ------------------------------------------------------------ */
+
+/* Per-point log-likelihood  ll_i = log sum_j alpha_j N(x_i | mu_j, Sigma_j + S_i).
+ * Replaces DeconvGMM._e_step's density part (deconv/gmm/deconv_gmm.py:43-62,77),
+ * SGDDeconvGMMModule.forward (deconv/gmm/sgd_deconv_gmm.py:14-28) and the per-batch body of
+ * score_batch (deconv/gmm/online_deconv_gmm.py:190-205, deconv/gmm/sgd_gmm.py:228-242).
+ *   log_alpha [K] = log mixture weights; out_ll [N]; out_sum (optional, 2 doubles on device:
+ *   sum_i ll_i and the non-PD pair count); status (optional, 1 device int, zeroed here). */
+DGMM_API int dgmm_loglik_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                    const float* log_alpha, const float* mu, const float* Sigma,
+                    float* out_ll, double* out_sum, int* status,
+                    void* workspace, size_t workspace_bytes, void* stream);
+
+/* Fused E-step + M-step reductions: ll_i and the packed statistics above, in one pass.
+ * Replaces deconv/gmm/deconv_gmm.py:39-107 (E-step + the reductions of the M-step),
+ * deconv/gmm/batch_deconv_gmm.py:95-120, deconv/gmm/online_deconv_gmm.py:148-166 and the
+ * autograd backward of deconv/gmm/sgd_deconv_gmm.py:14-28 (deconv/gmm/sgd_gmm.py:181).
+ *   g [N] optional per-point weights (NULL = 1; = grad_output for the SGD backward);
+ *   resp_floor: 0 for EM/SGD, 10*eps for OnlineDeconvGMM (online_deconv_gmm.py:150);
+ *   out_ll [N] optional; out_stats [dgmm_stats_len(D,K)]. */
+DGMM_API int dgmm_estep_stats_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                         const float* log_alpha, const float* mu, const float* Sigma,
+                         const float* g, float resp_floor,
+                         float* out_ll, float* out_stats,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* Materialising E-step for small N: log r [N,K], b [N,K,D], B [N,K,D,D], ll [N].
+ * Replaces the return value of DeconvGMM._e_step (deconv/gmm/deconv_gmm.py:64-79) and
+ * SGDDeconvGMM.posterior_params (deconv/gmm/sgd_deconv_gmm.py:71-94).
+ * Any of out_log_r / out_b / out_B may be NULL to skip that output. */
+DGMM_API int dgmm_estep_full_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                        const float* log_alpha, const float* mu, const float* Sigma,
+                        float* out_log_r, float* out_b, float* out_B, float* out_ll, int* status,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* Closed-form EM parameter update from the (all-reduced) packed statistics, in place:
+ *   delta = Sigma s1/s0; mu += delta; Sigma += Sigma (S2/s0) Sigma - delta delta^T + 2 w I/s0;
+ *   alpha = s0/n_total.  Equals deconv/gmm/deconv_gmm.py:81-109 and
+ * deconv/gmm/batch_deconv_gmm.py:65-75 (identity: SURVEY.md Appendix C).
+ * alpha [K] and log_alpha [K] are both written. */
+DGMM_API int dgmm_mstep_update_f32(const float* stats, double n_total, float w, int D, int K,
+                          float* mu, float* Sigma, float* alpha, float* log_alpha, void* stream);
+
+/* Register-only FFMA chain used to measure the sustained FP32 roofline denominator on the
+ * box (MEASURED_PEAKS.json has no FP32 entry).  Launches one kernel on `stream`;
+ * returns the number of FLOPs it executes through *flops.  sink = 1 device float. */
+DGMM_API int dgmm_fp32_probe(float* sink, int iters, double* flops, void* stream);
+
+/* ---- host entry points (HOST buffers; copies inside) -------------------------------- */
+
+typedef struct dgmm_ctx dgmm_ctx;
+
+/* Creates a context on `device` that owns pinned staging buffers, device chunk buffers and
+ * two copy/compute streams sized for chunks of `chunk_points` points. */
+DGMM_API int dgmm_ctx_create(dgmm_ctx** out, int device, int D, int K, int64_t chunk_points);
+DGMM_API void dgmm_ctx_destroy(dgmm_ctx* ctx);
+
+/* One EM iteration over HOST data (X [N,D], S in `noise_layout`), streamed to the device in
+ * chunks with copy/compute overlap: E-step statistics over all chunks, then the M-step
+ * update; mu/Sigma/alpha (HOST, in/out) are updated in place and *ll_sum receives
+ * sum_i ll_i under the parameters the iteration started from (what BaseGMM.fit compares
+ * against tol, deconv/gmm/base.py:46-55).  *nonpd receives the non-PD pair count.
+ * Replaces one trip of the loop at deconv/gmm/base.py:46-55. */
+DGMM_API int dgmm_em_iteration_host(dgmm_ctx* ctx, const float* X, const float* S, int noise_layout, int64_t N,
+                           float w, float* alpha, float* mu, float* Sigma,
+                           double* ll_sum, int64_t* nonpd);
+
+/* sum_i ll_i (and optionally ll_i [N] on the host) for HOST data.
+ * Replaces score_batch (deconv/gmm/online_deconv_gmm.py:190-205, deconv/gmm/sgd_gmm.py:228-242). */
+DGMM_API int dgmm_score_host(dgmm_ctx* ctx, const float* X, const float* S, int noise_layout, int64_t N,
+                    const float* alpha, const float* mu, const float* Sigma,
+                    float* out_ll, double* ll_sum, int64_t* nonpd);
+
+/* ---- diagnostics (not part of the drop-in surface) ----------------------------------- */
+
+/* Overrides the automatic launch plan of the pair kernel; -1 = automatic for that field.
+ * sigp/accp: 0 registers, 1 shared memory, 2 global; rc: register-cap class. */
+DGMM_API int dgmm_debug_set_tuning(int sigp, int accp, int nslot, int pt, int nst, int blocks_per_sm, int rc,
+                                   int no_bulk);
+/* out[0..10] = sigp, accp, rc, GS, NSLOT, TPB, PT, NST, grid, smem bytes, use_bulk. */
+DGMM_API int dgmm_debug_get_plan(int mode, int D, int K, int64_t N, int noise_layout, int has_g, int* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGMM_B200_H */
