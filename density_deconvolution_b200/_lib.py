@@ -24,8 +24,8 @@ _ERRORS = {
 SYMBOLS = (
     "dgmm_abi_version", "dgmm_supported_dims", "dgmm_workspace_bytes", "dgmm_loglik_f32",
     "dgmm_estep_stats_f32", "dgmm_estep_full_f32", "dgmm_mstep_update_f32", "dgmm_fp32_probe",
-    "dgmm_ctx_create", "dgmm_ctx_destroy", "dgmm_em_iteration_host", "dgmm_score_host",
-    "dgmm_debug_set_tuning", "dgmm_debug_get_plan",
+    "dgmm_ctx_create", "dgmm_ctx_destroy", "dgmm_em_iteration_host", "dgmm_estep_stats_host", "dgmm_score_host",
+    "dgmm_debug_set_tuning", "dgmm_debug_get_plan", "dgmm_debug_pair_timing", "dgmm_debug_pair_times",
 )
 
 
@@ -84,12 +84,18 @@ def lib():
     L.dgmm_em_iteration_host.restype = i32
     L.dgmm_em_iteration_host.argtypes = [vp, vp, vp, i32, i64, f32, vp, vp, vp, ctypes.POINTER(f64),
                                          ctypes.POINTER(i64)]
+    L.dgmm_estep_stats_host.restype = i32
+    L.dgmm_estep_stats_host.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp, f32, vp]
     L.dgmm_score_host.restype = i32
     L.dgmm_score_host.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp, vp, ctypes.POINTER(f64), ctypes.POINTER(i64)]
     L.dgmm_debug_set_tuning.restype = i32
     L.dgmm_debug_set_tuning.argtypes = [i32] * 8
     L.dgmm_debug_get_plan.restype = i32
     L.dgmm_debug_get_plan.argtypes = [i32, i32, i32, i64, i32, i32, ctypes.POINTER(i32)]
+    L.dgmm_debug_pair_timing.restype = i32
+    L.dgmm_debug_pair_timing.argtypes = [i32]
+    L.dgmm_debug_pair_times.restype = i32
+    L.dgmm_debug_pair_times.argtypes = [ctypes.POINTER(f32), ctypes.POINTER(i32)]
     if L.dgmm_abi_version() != 1:
         raise DgmmError("libdgmm_b200.so ABI version mismatch")
     _lib = L

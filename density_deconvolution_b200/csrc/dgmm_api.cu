@@ -399,6 +399,36 @@ int check_common(const void* X, const void* S, int noise, int64_t N, int D, int 
     return 0;
 }
 
+// Optional per-launch timing of the pair kernel (bench.py's roofline line): CUDA events
+// recorded on the launching stream directly around the launch, kept in a ring.
+struct PairTiming {
+    bool on = false;
+    int count = 0;
+    static constexpr int kRing = 512;
+    cudaEvent_t a[kRing], b[kRing];
+    bool made = false;
+};
+PairTiming g_timing;
+
+int timing_begin(cudaStream_t st) {
+    if (!g_timing.on) return -1;
+    if (!g_timing.made) {
+        for (int i = 0; i < PairTiming::kRing; ++i) {
+            cudaEventCreate(&g_timing.a[i]);
+            cudaEventCreate(&g_timing.b[i]);
+        }
+        g_timing.made = true;
+    }
+    const int slot = g_timing.count % PairTiming::kRing;
+    cudaEventRecord(g_timing.a[slot], st);
+    return slot;
+}
+void timing_end(int slot, cudaStream_t st) {
+    if (slot < 0) return;
+    cudaEventRecord(g_timing.b[slot], st);
+    ++g_timing.count;
+}
+
 // Runs prepare + pair kernel; leaves partials in the workspace.  Returns the plan.
 int run_pair(int mode, const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
              const float* mu, const float* Sigma, const float* g, float resp_floor, float* out_ll, void* workspace,
@@ -427,7 +457,9 @@ int run_pair(int mode, const float* X, const float* S, int noise, int64_t N, int
     p.use_bulk = plan.use_bulk;
     p.resp_floor = resp_floor;
     void* args[] = {&p};
+    const int tslot = timing_begin(st);
     CUDA_TRY(cudaLaunchKernel(plan.kernel, dim3(plan.grid), dim3(plan.TPB), args, plan.smem, st));
+    timing_end(tslot, st);
     *plan_out = plan;
     *ws_out = ws;
     return 0;
@@ -461,6 +493,27 @@ size_t dgmm_workspace_bytes(int D, int K) {
 int dgmm_debug_set_tuning(int sigp, int accp, int nslot, int pt, int nst, int blocks_per_sm, int rc, int no_bulk) {
     g_tuning.sigp = sigp; g_tuning.accp = accp; g_tuning.nslot = nslot; g_tuning.pt = pt;
     g_tuning.nst = nst; g_tuning.blocks_per_sm = blocks_per_sm; g_tuning.rc = rc; g_tuning.no_bulk = no_bulk;
+    return 0;
+}
+
+// Diagnostics: switch per-launch timing of the pair kernel on/off (resets the record).
+int dgmm_debug_pair_timing(int enable) {
+    g_timing.on = enable != 0;
+    g_timing.count = 0;
+    return 0;
+}
+// Diagnostics: device times (ms) of the pair-kernel launches recorded since timing was switched
+// on (at most the last 512).  Synchronises on the recorded events.  *n in = capacity, out = count.
+int dgmm_debug_pair_times(float* out_ms, int* n) {
+    if (!out_ms || !n) return DGMM_ERR_BAD_ARG;
+    const int have = g_timing.count < PairTiming::kRing ? g_timing.count : PairTiming::kRing;
+    const int m = have < *n ? have : *n;
+    for (int i = 0; i < m; ++i) {
+        const int slot = (g_timing.count - m + i) % PairTiming::kRing;
+        CUDA_TRY(cudaEventSynchronize(g_timing.b[slot]));
+        CUDA_TRY(cudaEventElapsedTime(&out_ms[i], g_timing.a[slot], g_timing.b[slot]));
+    }
+    *n = m;
     return 0;
 }
 
@@ -687,6 +740,52 @@ static int stream_chunks(dgmm_ctx* c, const float* X, const float* S, int layout
 
 extern "C" {
 
+static int upload_params(dgmm_ctx* c, const float* alpha, const float* mu, const float* Sigma) {
+    const int D = c->D, K = c->K;
+    cudaStream_t st = c->comp_st;
+    CUDA_TRY(cudaMemcpyAsync(c->d_alpha, alpha, (size_t)K * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->d_mu, mu, (size_t)K * D * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(c->d_Sigma, Sigma, (size_t)K * D * D * 4, cudaMemcpyHostToDevice, st));
+    log_kernel<<<(K + 127) / 128, 128, 0, st>>>(c->d_alpha, c->d_log_alpha, K);
+    return (int)cudaGetLastError();
+}
+
+// Streams (X, S) through the chunk buffers and leaves the accumulated packed statistics in
+// c->d_stats (compute stream, not synchronised).
+static int stats_pass_host(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, float resp_floor) {
+    const int D = c->D, K = c->K;
+    cudaStream_t st = c->comp_st;
+    CUDA_TRY(cudaMemsetAsync(c->d_stats, 0, dgmm_stats_len(D, K) * 4, st));
+    return stream_chunks(c, X, S, layout, N, [&](int, int64_t, int64_t n, const float* dX, const float* dS) -> int {
+        Plan plan;
+        Workspace ws;
+        int r = run_pair(MODE_STATS, dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr,
+                         resp_floor, nullptr, c->ws, c->ws_bytes, st, &plan, &ws);
+        if (r) return r;
+        const int total = K * (1 + D + D * D) + 1;
+        finalize_stats_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
+                                                                   plan.GS, plan.accp == ST_GLOBAL ? plan.TPB : plan.GS,
+                                                                   plan.accp == ST_GLOBAL ? plan.NSLOT : 1, c->d_stats, 1);
+        return (int)cudaGetLastError();
+    });
+}
+
+int dgmm_estep_stats_host(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, const float* alpha,
+                          const float* mu, const float* Sigma, float resp_floor, float* out_stats) {
+    if (!c || !alpha || !mu || !Sigma || !out_stats) return DGMM_ERR_BAD_ARG;
+    if (layout < 0 || layout > 3) return DGMM_ERR_LAYOUT;
+    if (layout == DGMM_NOISE_SHARED && c->chunk < c->D) return DGMM_ERR_BAD_ARG;
+    CUDA_TRY(cudaSetDevice(c->device));
+    int rc = upload_params(c, alpha, mu, Sigma);
+    if (rc) return rc;
+    rc = stats_pass_host(c, X, S, layout, N, resp_floor);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(out_stats, c->d_stats, dgmm_stats_len(c->D, c->K) * 4, cudaMemcpyDeviceToHost,
+                             c->comp_st));
+    CUDA_TRY(cudaStreamSynchronize(c->comp_st));
+    return 0;
+}
+
 int dgmm_em_iteration_host(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, float w, float* alpha,
                            float* mu, float* Sigma, double* ll_sum, int64_t* nonpd) {
     if (!c || !alpha || !mu || !Sigma) return DGMM_ERR_BAD_ARG;
@@ -695,35 +794,23 @@ int dgmm_em_iteration_host(dgmm_ctx* c, const float* X, const float* S, int layo
     CUDA_TRY(cudaSetDevice(c->device));
     const int D = c->D, K = c->K;
     cudaStream_t st = c->comp_st;
-    CUDA_TRY(cudaMemcpyAsync(c->d_alpha, alpha, (size_t)K * 4, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(c->d_mu, mu, (size_t)K * D * 4, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(c->d_Sigma, Sigma, (size_t)K * D * D * 4, cudaMemcpyHostToDevice, st));
-    log_kernel<<<(K + 127) / 128, 128, 0, st>>>(c->d_alpha, c->d_log_alpha, K);
-    CUDA_TRY(cudaMemsetAsync(c->d_stats, 0, dgmm_stats_len(D, K) * 4, st));
-    int rc = stream_chunks(c, X, S, layout, N, [&](int, int64_t, int64_t n, const float* dX, const float* dS) -> int {
-        Plan plan;
-        Workspace ws;
-        int r = run_pair(MODE_STATS, dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr, 0.f,
-                         nullptr, c->ws, c->ws_bytes, st, &plan, &ws);
-        if (r) return r;
-        const int total = K * (1 + D + D * D) + 1;
-        finalize_stats_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
-                                                                   plan.GS, plan.accp == ST_GLOBAL ? plan.TPB : plan.GS,
-                                                                   plan.accp == ST_GLOBAL ? plan.NSLOT : 1, c->d_stats, 1);
-        return (int)cudaGetLastError();
-    });
+    int rc = upload_params(c, alpha, mu, Sigma);
     if (rc) return rc;
+    rc = stats_pass_host(c, X, S, layout, N, 0.f);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(c->h_tail, c->d_stats + (size_t)K * (1 + D + D * D), 4 * sizeof(float),
+                             cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const bool bad = c->h_tail[3] > 0.f;
+    if (ll_sum) *ll_sum = bad ? -INFINITY : (double)c->h_tail[0] + (double)c->h_tail[1];
+    if (nonpd) *nonpd = (int64_t)c->h_tail[3];
+    if (bad) return 0;  // parameters stay as they were (deconv/gmm/base.py:48-49)
     rc = dgmm_mstep_update_f32(c->d_stats, (double)N, w, D, K, c->d_mu, c->d_Sigma, c->d_alpha, c->d_log_alpha, st);
     if (rc) return rc;
     CUDA_TRY(cudaMemcpyAsync(alpha, c->d_alpha, (size_t)K * 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaMemcpyAsync(mu, c->d_mu, (size_t)K * D * 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaMemcpyAsync(Sigma, c->d_Sigma, (size_t)K * D * D * 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaMemcpyAsync(c->h_tail, c->d_stats + (size_t)K * (1 + D + D * D), 4 * sizeof(float),
-                             cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    if (ll_sum) *ll_sum = (double)c->h_tail[0] + (double)c->h_tail[1];
-    if (nonpd) *nonpd = (int64_t)c->h_tail[3];
-    if (c->h_tail[3] > 0.f && ll_sum) *ll_sum = -INFINITY;
     return 0;
 }
 
@@ -734,10 +821,7 @@ int dgmm_score_host(dgmm_ctx* c, const float* X, const float* S, int layout, int
     CUDA_TRY(cudaSetDevice(c->device));
     const int D = c->D, K = c->K;
     cudaStream_t st = c->comp_st;
-    CUDA_TRY(cudaMemcpyAsync(c->d_alpha, alpha, (size_t)K * 4, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(c->d_mu, mu, (size_t)K * D * 4, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(c->d_Sigma, Sigma, (size_t)K * D * D * 4, cudaMemcpyHostToDevice, st));
-    log_kernel<<<(K + 127) / 128, 128, 0, st>>>(c->d_alpha, c->d_log_alpha, K);
+    { int rcp = upload_params(c, alpha, mu, Sigma); if (rcp) return rcp; }
     CUDA_TRY(cudaMemsetAsync(c->d_sum, 0, 2 * sizeof(double), st));
     int rc = stream_chunks(c, X, S, layout, N, [&](int idx, int64_t off, int64_t n, const float* dX, const float* dS) -> int {
         float* dll = c->d_ll[idx & 1];  // safe to reuse: its D2H copy two chunks ago is ordered on `st`

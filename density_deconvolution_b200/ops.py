@@ -173,6 +173,19 @@ def get_plan(mode, D, K, N, noise="full", has_g=False):
     return dict(zip(keys, list(out)))
 
 
+def pair_timing(enable=True):
+    """Start (or stop) recording the device time of every pair-kernel launch."""
+    check(_lib.lib().dgmm_debug_pair_timing(int(bool(enable))), "pair_timing")
+
+
+def pair_times(capacity=512):
+    """Device times (ms) of the pair-kernel launches recorded since ``pair_timing(True)``."""
+    buf = (ctypes.c_float * capacity)()
+    n = ctypes.c_int(capacity)
+    check(_lib.lib().dgmm_debug_pair_times(buf, ctypes.byref(n)), "pair_times")
+    return [buf[i] for i in range(n.value)]
+
+
 def fp32_probe(device, iters=4096, reps=5):
     """Measured FP32-FMA throughput (FLOP/s) of a register-only FFMA chain on ``device``."""
     sink = torch.zeros(1, dtype=torch.float32, device=device)
@@ -191,3 +204,76 @@ def fp32_probe(device, iters=4096, reps=5):
             torch.cuda.synchronize(device)
             best = max(best, flops.value / (a.elapsed_time(b) * 1e-3))
     return best
+
+
+class HostContext:
+    """Host-buffer entry points of the C ABI (``dgmm_ctx_*``, ``dgmm_em_iteration_host``,
+    ``dgmm_estep_stats_host``, ``dgmm_score_host``): data and parameters are CPU tensors
+    (pinned memory makes the chunked upload overlap with compute), every call streams the table
+    to the GPU and returns with the result on the host."""
+
+    def __init__(self, D, K, chunk_points=1 << 18, device=0):
+        self.D, self.K = int(D), int(K)
+        self.device = int(device)
+        self._ctx = ctypes.c_void_p(0)
+        check(_lib.lib().dgmm_ctx_create(ctypes.byref(self._ctx), self.device, self.D, self.K, int(chunk_points)),
+              "dgmm_ctx_create")
+
+    def close(self):
+        if self._ctx:
+            _lib.lib().dgmm_ctx_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    @staticmethod
+    def _host(t, name, shape=None):
+        if not isinstance(t, torch.Tensor) or t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+            raise DgmmError("%s must be a contiguous float32 CPU tensor" % name)
+        if shape is not None and tuple(t.shape) != tuple(shape):
+            raise ValueError("%s has shape %s, expected %s" % (name, tuple(t.shape), tuple(shape)))
+        return ctypes.c_void_p(t.data_ptr())
+
+    def _data(self, X, S, noise):
+        code = NOISE_LAYOUTS[noise] if isinstance(noise, str) else int(noise)
+        N = X.shape[0]
+        want = {_lib.NOISE_FULL: (N, self.D, self.D), _lib.NOISE_DIAG: (N, self.D), _lib.NOISE_SHARED: (self.D, self.D)}
+        pX = self._host(X, "X", (N, self.D))
+        pS = self._host(S, "noise_covars", want[code]) if code != _lib.NOISE_NONE else ctypes.c_void_p(0)
+        return pX, pS, code, N
+
+    def em_iteration(self, X, S, w, alpha, mu, Sigma, noise="full"):
+        """One EM iteration; ``alpha [K]``, ``mu``, ``Sigma`` (CPU) are updated in place.
+        Returns ``(ll_sum, n_nonpd)``."""
+        pX, pS, code, N = self._data(X, S, noise)
+        ll, bad = ctypes.c_double(0.0), ctypes.c_int64(0)
+        check(_lib.lib().dgmm_em_iteration_host(
+            self._ctx, pX, pS, code, N, float(w), self._host(alpha, "alpha", (self.K,)),
+            self._host(mu, "means", (self.K, self.D)), self._host(Sigma, "covars", (self.K, self.D, self.D)),
+            ctypes.byref(ll), ctypes.byref(bad)), "dgmm_em_iteration_host")
+        return ll.value, bad.value
+
+    def estep_stats(self, X, S, alpha, mu, Sigma, resp_floor=0.0, noise="full", out=None):
+        pX, pS, code, N = self._data(X, S, noise)
+        if out is None:
+            out = torch.empty(stats_len(self.D, self.K), dtype=torch.float32)
+        check(_lib.lib().dgmm_estep_stats_host(
+            self._ctx, pX, pS, code, N, self._host(alpha, "alpha", (self.K,)),
+            self._host(mu, "means", (self.K, self.D)), self._host(Sigma, "covars", (self.K, self.D, self.D)),
+            float(resp_floor), self._host(out, "out_stats", (stats_len(self.D, self.K),))), "dgmm_estep_stats_host")
+        return out
+
+    def score(self, X, S, alpha, mu, Sigma, noise="full", want_ll=False):
+        pX, pS, code, N = self._data(X, S, noise)
+        ll = torch.empty(N, dtype=torch.float32) if want_ll else None
+        tot, bad = ctypes.c_double(0.0), ctypes.c_int64(0)
+        check(_lib.lib().dgmm_score_host(
+            self._ctx, pX, pS, code, N, self._host(alpha, "alpha", (self.K,)), self._host(mu, "means", (self.K, self.D)),
+            self._host(Sigma, "covars", (self.K, self.D, self.D)),
+            self._host(ll, "out_ll") if want_ll else ctypes.c_void_p(0), ctypes.byref(tot), ctypes.byref(bad)),
+            "dgmm_score_host")
+        return (tot.value, bad.value, ll) if want_ll else (tot.value, bad.value)

@@ -150,6 +150,15 @@ DGMM_API int dgmm_em_iteration_host(dgmm_ctx* ctx, const float* X, const float* 
                            float w, float* alpha, float* mu, float* Sigma,
                            double* ll_sum, int64_t* nonpd);
 
+/* E-step statistics over HOST data without the parameter update: out_stats (HOST,
+ * dgmm_stats_len(D,K) floats) receives the packed buffer, ready for a cross-GPU all-reduce
+ * followed by dgmm_mstep_update_f32.  alpha/mu/Sigma are HOST inputs.  This is the per-rank
+ * half of dgmm_em_iteration_host for the sharded (one process per GPU) case and the body of
+ * OnlineDeconvGMM's per-minibatch step (resp_floor = 10 eps, online_deconv_gmm.py:150). */
+DGMM_API int dgmm_estep_stats_host(dgmm_ctx* ctx, const float* X, const float* S, int noise_layout, int64_t N,
+                          const float* alpha, const float* mu, const float* Sigma, float resp_floor,
+                          float* out_stats);
+
 /* sum_i ll_i (and optionally ll_i [N] on the host) for HOST data.
  * Replaces score_batch (deconv/gmm/online_deconv_gmm.py:190-205, deconv/gmm/sgd_gmm.py:228-242). */
 DGMM_API int dgmm_score_host(dgmm_ctx* ctx, const float* X, const float* S, int noise_layout, int64_t N,
@@ -164,6 +173,13 @@ DGMM_API int dgmm_debug_set_tuning(int sigp, int accp, int nslot, int pt, int ns
                                    int no_bulk);
 /* out[0..10] = sigp, accp, rc, GS, NSLOT, TPB, PT, NST, grid, smem bytes, use_bulk. */
 DGMM_API int dgmm_debug_get_plan(int mode, int D, int K, int64_t N, int noise_layout, int has_g, int* out);
+
+/* Per-launch device timing of the pair kernel (CUDA events on the launching stream, recorded
+ * directly around the launch).  dgmm_debug_pair_timing(1) starts a fresh record;
+ * dgmm_debug_pair_times returns the last min(*n, 512) launch times in ms (*n: in = capacity,
+ * out = count) after synchronising on them.  Used by bench.py's roofline line. */
+DGMM_API int dgmm_debug_pair_timing(int enable);
+DGMM_API int dgmm_debug_pair_times(float* out_ms, int* n);
 
 #ifdef __cplusplus
 }

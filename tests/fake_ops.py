@@ -1,0 +1,108 @@
+"""TEST DOUBLE for ``density_deconvolution_b200.ops`` built on the CPU oracle.
+
+The product has no CPU path.  The ``-m "not gpu"`` tests of the HOST logic (estimator loops,
+statistics algebra, the all-reduce plumbing under gloo) monkeypatch
+``density_deconvolution_b200.estimators._ops`` with this module so that the same estimator code
+runs on CPU tensors; the numbers come from ``oracle/gmm_oracle.py`` (float64, cast to float32
+at the boundary like the real kernels' outputs).  Never imported by the package itself."""
+import math
+
+import numpy as np
+import torch
+
+from oracle import gmm_oracle as orc
+
+
+def stats_len(D, K):
+    return K * (1 + D + D * D) + 4
+
+
+def _np(t):
+    return None if t is None else t.detach().cpu().numpy().astype(np.float64)
+
+
+def _full_noise(X, S, noise):
+    N, D = X.shape
+    if noise == "full":
+        return _np(S)
+    if noise == "diag":
+        s = _np(S)
+        out = np.zeros((N, D, D))
+        out[:, np.arange(D), np.arange(D)] = s
+        return out
+    if noise == "shared":
+        return np.broadcast_to(_np(S), (N, D, D)).copy()
+    return np.zeros((N, D, D))
+
+
+def loglik(X, S, log_alpha, mu, Sigma, noise="full", want_sum=False):
+    Sn = _full_noise(X, S, noise)
+    N = X.shape[0]
+    bad = 0
+    try:
+        ll = orc.loglik(_np(X), Sn, np.exp(_np(log_alpha)), _np(mu), _np(Sigma)) if N else np.zeros(0)
+    except np.linalg.LinAlgError:
+        ll, bad = np.full(N, -math.inf), 1
+    out = torch.tensor(ll, dtype=torch.float32, device=X.device)
+    if want_sum:
+        return out, torch.tensor([float(np.sum(ll)), float(bad)], dtype=torch.float64, device=X.device)
+    return out
+
+
+def estep_stats(X, S, log_alpha, mu, Sigma, g=None, resp_floor=0.0, noise="full", want_ll=True, out_stats=None):
+    N, D = X.shape
+    K = mu.shape[0]
+    Sn = _full_noise(X, S, noise)
+    buf = np.zeros(stats_len(D, K))
+    ll = np.zeros(0)
+    if N:
+        try:
+            s0, s1, S2, ll = orc.suff_stats(_np(X), Sn, np.exp(_np(log_alpha)), _np(mu), _np(Sigma), g=_np(g),
+                                            resp_floor=resp_floor)
+            buf[:K] = s0
+            buf[K:K + K * D] = s1.reshape(-1)
+            buf[K + K * D:K + K * D + K * D * D] = S2.reshape(-1)
+            tot = float(ll.sum())
+            hi = float(np.float32(tot))
+            buf[-4], buf[-3] = hi, tot - hi
+            buf[-2] = float(_np(g).sum()) if g is not None else float(N)
+        except np.linalg.LinAlgError:
+            ll = np.full(N, -math.inf)
+            buf[-4], buf[-1] = -math.inf, 1.0
+    st = torch.tensor(buf, dtype=torch.float32, device=X.device)
+    if out_stats is not None:
+        out_stats.copy_(st)
+        st = out_stats
+    return (torch.tensor(ll, dtype=torch.float32, device=X.device) if want_ll else None), st
+
+
+def estep_full(X, S, log_alpha, mu, Sigma, noise="full", want_means=True, want_covars=True):
+    Sn = _full_noise(X, S, noise)
+    N, D = X.shape
+    K = mu.shape[0]
+    dev = X.device
+    ll_sum, exp, ll = orc.e_step(_np(X), Sn, np.exp(_np(log_alpha)), _np(mu), _np(Sigma))
+    if exp is None:
+        nan = torch.full((N, K), float("nan"), device=dev)
+        return torch.full((N,), -math.inf, device=dev), nan, None, None, torch.ones(1, dtype=torch.int32, device=dev)
+    f = lambda a: torch.tensor(a, dtype=torch.float32, device=dev)  # noqa: E731
+    return (f(ll), f(exp[0]), f(exp[1]) if want_means else None, f(exp[2]) if want_covars else None,
+            torch.zeros(1, dtype=torch.int32, device=dev))
+
+
+def unpack_stats(stats, D, K):
+    o = 0
+    s0 = stats[o:o + K]; o += K
+    s1 = stats[o:o + K * D].view(K, D); o += K * D
+    S2 = stats[o:o + K * D * D].view(K, D, D); o += K * D * D
+    return s0, s1, S2, stats[o:o + 4]
+
+
+def mstep_update(stats, n_total, w, mu, Sigma, alpha, log_alpha):
+    K, D = mu.shape
+    s0, s1, S2, _ = unpack_stats(stats, D, K)
+    wts, means, covars = orc.m_step_from_stats(_np(s0), _np(s1), _np(S2), _np(mu), _np(Sigma), n_total, w)
+    mu.copy_(torch.tensor(means, dtype=torch.float32))
+    Sigma.copy_(torch.tensor(covars, dtype=torch.float32))
+    alpha.copy_(torch.tensor(wts[:, 0], dtype=torch.float32))
+    log_alpha.copy_(torch.log(alpha))
