@@ -133,9 +133,11 @@ class DeconvGMM:
         cond_covars = torch.eye(self.d, device=self.device).expand(n, self.k, self.d, self.d)
         return (log_resps, cond_means, cond_covars)
 
-    def _init_from_labels(self, X, resps):
+    def _init_from_labels(self, X, resps, centroids=None):
         """The M-step the reference applies to the k-means expectations (cond_means = X,
-        cond_covars = I; deconv_gmm.py:21-34,81-109) without the ``[N,K,D,D]`` broadcast."""
+        cond_covars = I; deconv_gmm.py:21-34,81-109) without the ``[N,K,D,D]`` broadcast.
+        An empty cluster (NaN parameters in the reference) is seeded with one pseudo-point at
+        its centroid."""
         n_total = _global_count(X.shape[0], self.device)
         s0 = resps.sum(dim=0)                                          # [K]
         sx = resps.t() @ X                                             # [K,D]
@@ -143,6 +145,11 @@ class DeconvGMM:
         if _dist.is_distributed():
             for t in (s0, sx, sxx):
                 torch.distributed.all_reduce(t)
+        if centroids is not None:
+            empty = s0 <= 0
+            s0 = torch.where(empty, torch.ones_like(s0), s0)
+            sx = torch.where(empty[:, None], centroids, sx)
+            sxx = torch.where(empty[:, None, None], centroids[:, :, None] * centroids[:, None, :], sxx)
         means = sx / s0[:, None]
         eye = torch.eye(self.d, device=self.device)
         scatter = sxx - s0[:, None, None] * means[:, :, None] * means[:, None, :]
@@ -154,7 +161,8 @@ class DeconvGMM:
         X, S, layout = self._prep(data)
         n_total = _global_count(X.shape[0], self.device)
         if init:
-            self._init_from_labels(X, self._kmeans_init(X))
+            resps, centroids = k_means(X, self.k, 50, 1e-9, self.device)
+            self._init_from_labels(X, resps, centroids)
         mix = self._mixture()
         stats = torch.empty(_ops.stats_len(self.d, self.k), dtype=torch.float32, device=self.device)
         prev = -math.inf

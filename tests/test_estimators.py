@@ -33,6 +33,7 @@ def t32(a, device):
 
 def close(got, want, rtol=P_RTOL):
     got = got.detach().cpu().numpy().astype(np.float64) if torch.is_tensor(got) else np.asarray(got, np.float64)
+    want = want.detach().cpu().numpy() if torch.is_tensor(want) else want
     want = np.asarray(want, dtype=np.float64)
     assert got.shape == want.shape, (got.shape, want.shape)
     err = np.max(np.abs(got - want))
