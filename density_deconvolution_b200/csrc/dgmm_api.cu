@@ -456,6 +456,12 @@ int run_pair(int mode, const float* X, const float* S, int noise, int64_t N, int
     p.K = K; p.GS = GS; p.NSLOT = plan.NSLOT; p.PT = plan.PT; p.NST = plan.NST; p.noise = noise;
     p.use_bulk = plan.use_bulk;
     p.resp_floor = resp_floor;
+    {
+        const StageLayout SL = stage_layout(D, noise, plan.PT, g != nullptr);
+        p.n_s = noise_floats_per_point(D, noise);
+        p.off_X = SL.off_X; p.off_g = SL.off_g; p.stage_bytes = SL.bytes;
+        p.rounds = plan.PT / plan.NSLOT;
+    }
     void* args[] = {&p};
     const int tslot = timing_begin(st);
     CUDA_TRY(cudaLaunchKernel(plan.kernel, dim3(plan.grid), dim3(plan.TPB), args, plan.smem, st));

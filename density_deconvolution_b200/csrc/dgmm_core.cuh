@@ -7,6 +7,15 @@
 // What the reference does with batched LAPACK calls on materialised [N,K,D,D] tensors
 // (deconv/gmm/deconv_gmm.py:43-62: cholesky, cholesky_solve(I), matmuls) is done here in
 // place on D(D+1)/2 floats:
+// Pair kernel (hot path) -- square-root-free, inverse-free formulation:
+//   ldl_forward     : T = L D L^T (unit lower L, right-looking), y = L^{-1} d carried along,
+//                     sum log2 of the pivots; the diagonal is left holding 1/D_kk.
+//   ldl_back_solve  : u = L^{-T} D^{-1} y = T^{-1} d (back substitution, no inverse needed).
+//   ldl_scaled_inverse : L, 1/D -> c * T^{-1} (lower triangle) in place by the Takahashi
+//                     recurrence Z = D^{-1} L^{-1} + (I - L^T) Z, bottom row upwards; neither
+//                     L^{-1} nor any extra multiply per element is formed (c folds the
+//                     responsibility weight in for free).
+// Materialising kernel (API-parity path, dgmm_full.cuh) -- classic Cholesky route:
 //   chol_forward : T = L L^T (right-looking), y = L^{-1} d carried as an extra row,
 //                  sum log2 of the pivots; the diagonal is left holding 1/L_kk.
 //   tri_inverse  : L -> L^{-1} in place.
@@ -65,6 +74,16 @@ DGMM_HD float mufu_rsqrt(float x) {
     return r;
 #else
     return 1.0f / sqrtf(x);
+#endif
+}
+
+DGMM_HD float mufu_rcp(float x) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#else
+    return 1.0f / x;
 #endif
 }
 

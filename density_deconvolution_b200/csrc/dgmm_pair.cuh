@@ -37,7 +37,7 @@ enum : int { NOISE_FULL = 0, NOISE_DIAG = 1, NOISE_NONE = 2, NOISE_SHARED = 3 };
 
 constexpr int kMaxStages = 4;
 constexpr int kPairMaxThreads = 256;  // largest block the pair kernel is compiled for
-constexpr int kSmemHeader = 1152;  // mbarriers (64 B) + logsumexp exchange (512 B) + double reduce (512 B)
+constexpr int kSmemHeader = 1152;  // mbarriers (64 B) + logsumexp exchange (2 x 256 B) + double reduce (512 B)
 
 struct PairParams {
     const float* X;          // [N,D]
@@ -55,6 +55,11 @@ struct PairParams {
     int K, GS, NSLOT, PT, NST, noise;
     int use_bulk;
     float resp_floor;
+    // derived on the host (constant-bank operands in the kernel): ring-stage layout and loop counts
+    int n_s;          // noise floats per point in the tile (D*D | D | 0)
+    int off_X, off_g; // byte offsets of the X and g sub-tiles inside a stage (S sits at 0)
+    int stage_bytes;
+    int rounds;       // PT / NSLOT
 };
 
 // ---------------------------------------------------------------------------------------
