@@ -12,12 +12,11 @@
 #include <vector>
 
 #include "../../include/dgmm_b200.h"
-#include "dgmm_pair.cuh"
-#include "dgmm_full.cuh"
+#include "dgmm_tables.cuh"
 
 // per-D lookup functions, one translation unit each (dgmm_inst_dXX.cu)
-#define DGMM_DECL(D)                                                       \
-    const void* dgmm_pair_lookup_d##D(int mode, int sigp, int accp, int rc); \
+#define DGMM_DECL(D)                                                          \
+    dgmm::PairVariant dgmm_pair_lookup_d##D(int mode, int which, int gcls, int nz); \
     const void* dgmm_full_lookup_d##D();
 DGMM_DECL(1) DGMM_DECL(2) DGMM_DECL(3) DGMM_DECL(4) DGMM_DECL(5) DGMM_DECL(6) DGMM_DECL(7) DGMM_DECL(8)
 DGMM_DECL(9) DGMM_DECL(10) DGMM_DECL(11) DGMM_DECL(12) DGMM_DECL(13) DGMM_DECL(14) DGMM_DECL(15) DGMM_DECL(16)
@@ -29,7 +28,7 @@ namespace {
 
 using namespace dgmm;
 
-typedef const void* (*pair_lookup_t)(int, int, int, int);
+typedef PairVariant (*pair_lookup_t)(int, int, int, int);
 typedef const void* (*full_lookup_t)();
 
 #define DGMM_ROW(D) {dgmm_pair_lookup_d##D, dgmm_full_lookup_d##D}
@@ -286,13 +285,15 @@ __global__ void __launch_bounds__(256) fp32_probe_kernel(float* sink, int iters)
 // launch planning for the pair kernel
 // ---------------------------------------------------------------------------------------
 struct Tuning {
+    // sigp/accp both ST_GLOBAL (2) force the fallback variant; rc selects the placement
+    // (0 = main, 1 = alternative); the rest override the tile geometry.  -1 = automatic.
     int sigp = -1, accp = -1, nslot = -1, pt = -1, nst = -1, blocks_per_sm = -1, rc = -1, no_bulk = 0;
 };
 Tuning g_tuning;
 
 struct Plan {
     const void* kernel = nullptr;
-    int sigp, accp, rc, GS, NSLOT, TPB, PT, NST, grid, use_bulk;
+    int sigp, accp, rc, GS, NSLOT, TPB, PT, NST, grid, use_bulk, gcls;
     size_t smem;
     long long n_tiles;
 };
@@ -308,67 +309,71 @@ size_t pair_smem_bytes(int D, int noise, bool has_g, int sigp, int accp, int GS,
     return b;
 }
 
+inline int group_class(int GS) {
+    if (GS < 32) return GCLS_SUB;
+    if (GS == 32) return GCLS_WARP;
+    return GS <= 128 ? GCLS_MW4 : GCLS_MWN;
+}
+
+// Tile geometry for one variant; returns false when it cannot be made to fit.
+bool fit_geometry(const DeviceInfo& dev, const PairVariant& v, int mode, int D, int noise, bool has_g, Plan* p) {
+    const Tuning& t = g_tuning;
+    const int GS = p->GS;
+    int nslot = std::max(1, 128 / GS);
+    if (t.nslot > 0) nslot = t.nslot;
+    if (GS > 32 && nslot > 15) nslot = 15;            // named barriers 1..15
+    while (GS * nslot > v.max_threads && nslot > 1) --nslot;
+    if (GS * nslot > v.max_threads) return false;
+    while (GS * nslot < 32) ++nslot;                   // whole warps only (full-mask shuffles)
+    const int pt0 = (D <= 10) ? 16 : (D <= 16 ? 8 : 4);
+    int nst = (D <= 16) ? 3 : 2;
+    if (t.nst > 0) nst = std::min(t.nst, kMaxStages);
+    for (;;) {
+        int PT = t.pt > 0 ? t.pt : pt0;
+        int lcm = nslot;                               // PT: a multiple of NSLOT and of 4
+        while (lcm % 4) lcm += nslot;
+        PT = ((PT + lcm - 1) / lcm) * lcm;
+        const size_t smem = pair_smem_bytes(D, noise, has_g, v.sigp, v.accp, GS, GS * nslot, PT, nst, mode);
+        if (smem <= (size_t)dev.smem_optin) {
+            p->NSLOT = nslot; p->TPB = GS * nslot; p->PT = PT; p->NST = nst; p->smem = smem;
+            return true;
+        }
+        if (GS >= 32 && nslot > 1) { nslot = 1; continue; }
+        if (GS < 32 && GS * nslot > 32) { nslot /= 2; continue; }
+        if (nst > 1) { --nst; continue; }
+        return false;
+    }
+}
+
 int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int noise, bool has_g,
               const void* X, const void* S, const void* g, Plan* out) {
     Plan p;
     p.GS = group_size(K);
+    p.gcls = group_class(p.GS);
     const Tuning& t = g_tuning;
-
-    // slots per block
-    if (p.GS <= 32) p.NSLOT = 128 / p.GS;
-    else p.NSLOT = std::max(1, 128 / p.GS);
-    if (t.nslot > 0) p.NSLOT = t.nslot;
-    if (p.GS > 32 && p.NSLOT > 15) p.NSLOT = 15;
-    while (p.GS * p.NSLOT > kPairMaxThreads) --p.NSLOT;
-    if (p.NSLOT < 1) return DGMM_ERR_UNSUPPORTED_K;
-
-    // placement of Sigma_j and of the accumulators
-    // (measured on B200, profiles/r01_variant_sweep.md)
-    if (D <= 12) { p.sigp = ST_SMEM; p.accp = ST_REG; p.rc = (mode == MODE_STATS) ? 1 : 2; }
-    else if (D <= DGMM_UNROLL_D) { p.sigp = (mode == MODE_STATS) ? ST_GLOBAL : ST_SMEM; p.accp = ST_SMEM; p.rc = 0; }
-    else { p.sigp = ST_GLOBAL; p.accp = ST_GLOBAL; p.rc = 0; }
-    if (t.sigp >= 0) p.sigp = t.sigp;
-    if (t.accp >= 0) p.accp = t.accp;
+    const bool force_fallback = (t.sigp == ST_GLOBAL && t.accp == ST_GLOBAL);
+    int which = (t.rc == 1) ? 1 : 0;
+    PairVariant v{nullptr, 0, 0, 0, 0, 0, 0};
+    const int nz = (noise == NOISE_FULL) ? NZ_FULL : NZ_DIAG;
+    bool ok = false;
+    if (!force_fallback) {
+        v = kDims[D].pair(mode, which, p.gcls, nz);
+        ok = v.fn && fit_geometry(dev, v, mode, D, noise, has_g, &p);
+        if (!ok && which == 1) {
+            which = 0;
+            v = kDims[D].pair(mode, 0, p.gcls, nz);
+            ok = v.fn && fit_geometry(dev, v, mode, D, noise, has_g, &p);
+        }
+    }
+    if (!ok) {
+        which = 2;
+        v = kDims[D].pair(mode, 2, GCLS_ANY, NZ_ANY);
+        if (!v.fn) return DGMM_ERR_UNSUPPORTED_D;
+        if (!fit_geometry(dev, v, mode, D, noise, has_g, &p)) return DGMM_ERR_UNSUPPORTED_K;
+    }
+    p.kernel = v.fn;
+    p.sigp = v.sigp; p.accp = v.accp; p.rc = which;
     if (mode == MODE_LOGLIK) p.accp = ST_GLOBAL;
-    if (t.rc >= 0) p.rc = t.rc;
-
-    // tile size and ring depth
-    const int pt0 = (D <= 10) ? 16 : (D <= 16 ? 8 : 4);
-    p.NST = (D <= 16) ? 3 : 2;
-    if (t.nst > 0) p.NST = std::min(t.nst, kMaxStages);
-
-    for (int attempt = 0; attempt < 16; ++attempt) {
-        while (p.GS * p.NSLOT < 32) ++p.NSLOT;  // whole warps only (full-mask shuffles)
-        p.TPB = p.GS * p.NSLOT;
-        int PT = t.pt > 0 ? t.pt : pt0;
-        // PT must be a multiple of NSLOT and of 4
-        int lcm = p.NSLOT;
-        while (lcm % 4) lcm += p.NSLOT;
-        PT = ((PT + lcm - 1) / lcm) * lcm;
-        p.PT = PT;
-        p.smem = pair_smem_bytes(D, noise, has_g, p.sigp, p.accp, p.GS, p.TPB, p.PT, p.NST, mode);
-        if (p.smem <= (size_t)dev.smem_optin) break;
-        // does not fit: shrink in this order
-        if (p.NSLOT > 1 && p.GS >= 32) { p.NSLOT = 1; continue; }
-        if (p.GS < 32 && p.GS * p.NSLOT > 32) { p.NSLOT /= 2; continue; }
-        if (mode == MODE_STATS && p.accp == ST_SMEM) { p.accp = ST_GLOBAL; continue; }
-        if (p.sigp == ST_SMEM) { p.sigp = ST_GLOBAL; continue; }
-        if (p.NST > 1) { --p.NST; continue; }
-        return DGMM_ERR_UNSUPPORTED_K;
-    }
-    if (p.smem > (size_t)dev.smem_optin) return DGMM_ERR_UNSUPPORTED_K;
-
-    if (p.TPB > 128 && p.rc != 0) p.rc = 0;
-    p.kernel = kDims[D].pair(mode, p.sigp, p.accp, p.rc);
-    if (!p.kernel && p.rc != 0) { p.rc = 0; p.kernel = kDims[D].pair(mode, p.sigp, p.accp, 0); }
-    if (!p.kernel) {
-        // fall back to the universal placement (compiled for every D)
-        p.sigp = ST_GLOBAL;
-        if (mode == MODE_STATS) p.accp = ST_GLOBAL;
-        p.smem = pair_smem_bytes(D, noise, has_g, p.sigp, p.accp, p.GS, p.TPB, p.PT, p.NST, mode);
-        p.kernel = kDims[D].pair(mode, p.sigp, p.accp, 0);
-        if (!p.kernel) return DGMM_ERR_UNSUPPORTED_D;
-    }
 
     CUDA_TRY(cudaFuncSetAttribute(p.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
     int occ = 0;

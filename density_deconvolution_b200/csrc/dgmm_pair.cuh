@@ -27,6 +27,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 #include "dgmm_core.cuh"
 
 namespace dgmm {
@@ -104,6 +106,31 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// group classes of the pair kernel (see dgmm_pair_body.inc)
+enum : int { GCLS_SUB = 0, GCLS_WARP = 1, GCLS_MW4 = 2, GCLS_MWN = 3, GCLS_ANY = 4 };
+// noise classes of the pair kernel
+enum : int { NZ_FULL = 0, NZ_DIAG = 1, NZ_ANY = 2 };
+
+// predicated 32-bit global store (no branch in the instruction stream)
+__device__ __forceinline__ void st_global_if(float* ptr, float v, bool pred) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %2, 0;\n"
+        "@p st.global.f32 [%0], %1;\n"
+        "}\n" ::"l"(ptr), "f"(v), "r"((int)pred)
+        : "memory");
+}
+// an empty use of a register value
+__device__ __forceinline__ void keep_alive(float v) { asm volatile("" ::"f"(v)); }
+
+
+__device__ __forceinline__ float warp_max_f32(float v) {
+    float r;
+    asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));  // CREDUX.MAX.F32 (sm_100a)
+    return r;
 }
 
 // Bytes of one ring stage and the offsets of its three sub-tiles (all multiples of 16).

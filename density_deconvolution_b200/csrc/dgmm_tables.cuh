@@ -8,65 +8,72 @@
 
 namespace dgmm {
 
+// One compiled pair-kernel variant: the entry point plus the placement / launch bounds it was
+// instantiated with (the launch planner sizes shared memory and blocks from these).
+struct PairVariant {
+    const void* fn;
+    int sigp, accp, gcls, nz, max_threads, min_blocks;
+};
 
-// Returns the kernel for (mode, sigma placement, accumulator placement) or nullptr when
-// that combination is not compiled for this D.
-typedef const void* (*pair_lookup_fn)(int mode, int sigp, int accp, int rc);
+// Returns the variant for (mode, which, gcls); fn == nullptr when that combination is not compiled
+// for this D.  `which`: 0 = main placement, 1 = alternative placement (tuning sweeps),
+// 2 = universal fallback (Sigma and accumulators in global memory, any group size).
+typedef PairVariant (*pair_lookup_fn)(int mode, int which, int gcls, int nz);
 typedef const void* (*full_lookup_fn)();
 
-// Register-cap classes (launch bounds): rc 0 = <=256 threads, 255 registers;
-// rc 1 = <=128 threads, 3 blocks/SM (168 registers); rc 2 = <=128 threads, 4 blocks/SM (128).
-template <int D, int MODE, int SIGP, int ACCP, int RC>
-inline const void* pair_ptr() {
-    constexpr int MAXT = RC == 0 ? kPairMaxThreads : 128;
-    constexpr int MINB = RC == 0 ? 1 : (RC == 1 ? 3 : 4);
+template <int D, int MODE, int SIGP, int ACCP, int GCLS, int NZ, int MAXT, int MINB>
+inline PairVariant pair_variant() {
+    PairVariant v;
     if constexpr (D <= DGMM_UNROLL_D)
-        return reinterpret_cast<const void*>(&unrolled::pair_kernel<D, MODE, SIGP, ACCP, MAXT, MINB>);
+        v.fn = reinterpret_cast<const void*>(&unrolled::pair_kernel<D, MODE, SIGP, ACCP, GCLS, NZ, MAXT, MINB>);
     else
-        return reinterpret_cast<const void*>(&rolled::pair_kernel<D, MODE, SIGP, ACCP, MAXT, MINB>);
+        v.fn = reinterpret_cast<const void*>(&rolled::pair_kernel<D, MODE, SIGP, ACCP, GCLS, NZ, MAXT, MINB>);
+    v.sigp = SIGP; v.accp = ACCP; v.gcls = GCLS; v.nz = NZ; v.max_threads = MAXT; v.min_blocks = MINB;
+    return v;
 }
 
-template <int D, int MODE, int SIGP, int ACCP>
-inline const void* pair_ptr_rc(int rc, int max_rc) {
-    if (rc > max_rc) return nullptr;
-    if (rc == 0) return pair_ptr<D, MODE, SIGP, ACCP, 0>();
-    if constexpr (D <= DGMM_UNROLL_D) {
-        if (rc == 1) return pair_ptr<D, MODE, SIGP, ACCP, 1>();
+// The four group classes of one placement.  Groups wider than 128 lanes (GCLS_MWN) need blocks of
+// 256 threads, so that class is always compiled with the (256, 1) bounds.
+template <int D, int MODE, int SIGP, int ACCP, int NZ, int MAXT, int MINB>
+inline PairVariant pair_by_gcls_nz(int gcls) {
+    switch (gcls) {
+        case GCLS_SUB:  return pair_variant<D, MODE, SIGP, ACCP, GCLS_SUB, NZ, MAXT, MINB>();
+        case GCLS_WARP: return pair_variant<D, MODE, SIGP, ACCP, GCLS_WARP, NZ, MAXT, MINB>();
+        case GCLS_MW4:  return pair_variant<D, MODE, SIGP, ACCP, GCLS_MW4, NZ, MAXT, MINB>();
+        case GCLS_MWN:  return pair_variant<D, MODE, SIGP, ACCP, GCLS_MWN, NZ, kPairMaxThreads, 1>();
+        default: break;
     }
-    if constexpr (D <= 12) {
-        if (rc == 2) return pair_ptr<D, MODE, SIGP, ACCP, 2>();
-    }
-    return nullptr;
+    return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
 }
 
-// Which placements exist for which D (keep in sync with make_plan() in dgmm_api.cu):
-//   D <= 12      : Sigma {SMEM, REG} x acc {REG (Sigma SMEM only), SMEM}; rc 0..2
-//   13 <= D <= 16: Sigma {SMEM, GLOBAL} x acc {SMEM};                     rc 0..1
-//   every D      : GLOBAL/GLOBAL fallback (rc 0); D > 16 has nothing else (rolled loops)
+template <int D, int MODE, int SIGP, int ACCP, int MAXT, int MINB>
+inline PairVariant pair_by_gcls(int gcls, int nz) {
+    if (nz == NZ_FULL) return pair_by_gcls_nz<D, MODE, SIGP, ACCP, NZ_FULL, MAXT, MINB>(gcls);
+    return pair_by_gcls_nz<D, MODE, SIGP, ACCP, NZ_DIAG, MAXT, MINB>(gcls);
+}
+
+// Placements (measured on B200, profiles/):
+//   D <= 12      : Sigma_j in shared-memory columns, accumulators in registers;
+//                  STATS 128 threads x 3 blocks/SM (168 registers), LOGLIK x 4 blocks/SM (128)
+//   13 <= D <= 16: accumulators in shared-memory columns, Sigma_j from global/L1 (STATS) or shared
+//                  (LOGLIK), 255 registers
+//   D > 16       : fallback only (rolled loops, local-memory arrays)
 template <int D>
-inline const void* pair_lookup(int mode, int sigp, int accp, int rc) {
-    if (mode == MODE_LOGLIK) {
-        if constexpr (D <= 12) {
-            if (sigp == ST_REG) return pair_ptr_rc<D, MODE_LOGLIK, ST_REG, ST_GLOBAL>(rc, 2);
-        }
-        if constexpr (D <= DGMM_UNROLL_D) {
-            if (sigp == ST_SMEM) return pair_ptr_rc<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL>(rc, 2);
-        }
-        if (sigp == ST_GLOBAL) return pair_ptr_rc<D, MODE_LOGLIK, ST_GLOBAL, ST_GLOBAL>(rc, 0);
-        return nullptr;
+inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
+    if (which == 2) {
+        if (mode == MODE_LOGLIK)
+            return pair_variant<D, MODE_LOGLIK, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
+        return pair_variant<D, MODE_STATS, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
     }
+    if (which != 0) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};  // no alternative placements compiled
     if constexpr (D <= 12) {
-        if (sigp == ST_SMEM && accp == ST_REG) return pair_ptr_rc<D, MODE_STATS, ST_SMEM, ST_REG>(rc, 2);
-        if (sigp == ST_REG && accp == ST_SMEM) return pair_ptr_rc<D, MODE_STATS, ST_REG, ST_SMEM>(rc, 1);
+        if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 4>(gcls, nz);
+        return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_REG, 128, 3>(gcls, nz);
+    } else if constexpr (D <= DGMM_UNROLL_D) {
+        if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, kPairMaxThreads, 1>(gcls, nz);
+        return pair_by_gcls<D, MODE_STATS, ST_GLOBAL, ST_SMEM, kPairMaxThreads, 1>(gcls, nz);
     }
-    if constexpr (D <= DGMM_UNROLL_D) {
-        if (sigp == ST_SMEM && accp == ST_SMEM) return pair_ptr_rc<D, MODE_STATS, ST_SMEM, ST_SMEM>(rc, 2);
-    }
-    if constexpr (D > 12 && D <= DGMM_UNROLL_D) {
-        if (sigp == ST_GLOBAL && accp == ST_SMEM) return pair_ptr_rc<D, MODE_STATS, ST_GLOBAL, ST_SMEM>(rc, 1);
-    }
-    if (sigp == ST_GLOBAL && accp == ST_GLOBAL) return pair_ptr_rc<D, MODE_STATS, ST_GLOBAL, ST_GLOBAL>(rc, 0);
-    return nullptr;
+    return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
 }
 
 template <int D>
@@ -80,11 +87,11 @@ inline const void* full_lookup() {
 }  // namespace dgmm
 
 #define DGMM_DECLARE_DIM(D)                                                  \
-    extern "C++" const void* dgmm_pair_lookup_d##D(int mode, int sigp, int accp, int rc); \
+    extern "C++" dgmm::PairVariant dgmm_pair_lookup_d##D(int mode, int which, int gcls, int nz); \
     extern "C++" const void* dgmm_full_lookup_d##D();
 
 #define DGMM_DEFINE_DIM(D)                                                                      \
-    const void* dgmm_pair_lookup_d##D(int mode, int sigp, int accp, int rc) {                   \
-        return dgmm::pair_lookup<D>(mode, sigp, accp, rc);                                       \
+    dgmm::PairVariant dgmm_pair_lookup_d##D(int mode, int which, int gcls, int nz) {             \
+        return dgmm::pair_lookup<D>(mode, which, gcls, nz);                                      \
     }                                                                                           \
     const void* dgmm_full_lookup_d##D() { return dgmm::full_lookup<D>(); }

@@ -4,6 +4,7 @@ import re, subprocess, sys, os
 CSRC = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "density_deconvolution_b200", "csrc")
 D = int(sys.argv[1]); flt = sys.argv[2]; nofp = "--nofp" in sys.argv
 obj = os.path.join(CSRC, "build", "dgmm_inst_d%02d.o" % D)
+if "--obj" in sys.argv: obj = sys.argv[sys.argv.index("--obj") + 1]
 txt = subprocess.run(["cuobjdump", "-sass", obj], capture_output=True, text=True).stdout
 for f in re.split(r"\n\s*Function : ", txt)[1:]:
     name = subprocess.run(["c++filt", f.split("\n")[0].strip()], capture_output=True, text=True).stdout.strip()

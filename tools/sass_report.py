@@ -19,9 +19,11 @@ def demangle(n):
 
 def main():
     D = int(sys.argv[1])
-    rest = [a for a in sys.argv[2:] if not a.startswith("--")]
+    rest = [a for i, a in enumerate(sys.argv[2:]) if not a.startswith("--") and sys.argv[i + 1] != "--obj"]
     flt = rest[0] if rest else ""
     obj = os.path.join(CSRC, "build", "dgmm_inst_d%02d.o" % D)
+    if "--obj" in sys.argv:
+        obj = sys.argv[sys.argv.index("--obj") + 1]
     flags = "-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -fvisibility=hidden -Xptxas -v"
     if "--no-build" not in sys.argv:
         r = subprocess.run("nvcc %s -c dgmm_inst_d%02d.cu -o %s" % (flags, D, obj), shell=True, cwd=CSRC,
