@@ -293,7 +293,7 @@ Tuning g_tuning;
 
 struct Plan {
     const void* kernel = nullptr;
-    int sigp, accp, rc, GS, NSLOT, TPB, PT, NST, grid, use_bulk, gcls;
+    int sigp, accp, rc, GS, NSLOT, TPB, PT, NST, grid, use_bulk, gcls, tmem_cols;
     size_t smem;
     long long n_tiles;
 };
@@ -334,7 +334,9 @@ bool fit_geometry(const DeviceInfo& dev, const PairVariant& v, int mode, int D, 
         while (lcm % 4) lcm += nslot;
         PT = ((PT + lcm - 1) / lcm) * lcm;
         const size_t smem = pair_smem_bytes(D, noise, has_g, v.sigp, v.accp, GS, GS * nslot, PT, nst, mode);
-        if (smem <= (size_t)dev.smem_optin) {
+        const bool tmem_ok = v.accp != ST_TMEM || mode != MODE_STATS ||
+                             tmem_alloc_cols(ns_of(D), GS * nslot / 32) <= 512;
+        if (smem <= (size_t)dev.smem_optin && tmem_ok) {
             p->NSLOT = nslot; p->TPB = GS * nslot; p->PT = PT; p->NST = nst; p->smem = smem;
             return true;
         }
@@ -352,14 +354,14 @@ int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int no
     p.gcls = group_class(p.GS);
     const Tuning& t = g_tuning;
     const bool force_fallback = (t.sigp == ST_GLOBAL && t.accp == ST_GLOBAL);
-    int which = (t.rc == 1) ? 1 : 0;
+    int which = (t.rc > 0) ? t.rc : 0;
     PairVariant v{nullptr, 0, 0, 0, 0, 0, 0};
     const int nz = (noise == NOISE_FULL) ? NZ_FULL : NZ_DIAG;
     bool ok = false;
     if (!force_fallback) {
         v = kDims[D].pair(mode, which, p.gcls, nz);
         ok = v.fn && fit_geometry(dev, v, mode, D, noise, has_g, &p);
-        if (!ok && which == 1) {
+        if (!ok && which != 0) {
             which = 0;
             v = kDims[D].pair(mode, 0, p.gcls, nz);
             ok = v.fn && fit_geometry(dev, v, mode, D, noise, has_g, &p);
@@ -379,6 +381,25 @@ int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int no
     int occ = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, p.kernel, p.TPB, p.smem));
     if (occ < 1) return DGMM_ERR_UNSUPPORTED_K;
+    p.tmem_cols = 0;
+    if (mode == MODE_STATS && p.accp == ST_TMEM) {
+        // The occupancy query answers 1 block/SM for any kernel that allocates tensor memory, yet
+        // blocks whose columns fit side by side do run concurrently (tools/ubench_tmem.cu): derive
+        // the residency from registers, shared memory and the 512 TMEM columns instead.  All
+        // resident blocks must hold their columns at the same time (a block that cannot allocate
+        // would spin until another one exits).
+        p.tmem_cols = tmem_alloc_cols(ns_of(D), p.TPB / 32);
+        cudaFuncAttributes fa;
+        CUDA_TRY(cudaFuncGetAttributes(&fa, p.kernel));
+        const int regs_per_block = ((fa.numRegs + 7) & ~7) * p.TPB;
+        int smem_sm = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev.device));
+        int o = 65536 / std::max(regs_per_block, 1);
+        o = std::min<int>(o, smem_sm / (int)(p.smem + fa.sharedSizeBytes + 1024));
+        o = std::min(o, 2048 / p.TPB);
+        o = std::min(o, 512 / p.tmem_cols);
+        occ = std::max(o, 1);
+    }
     if (t.blocks_per_sm > 0) occ = std::min(occ, t.blocks_per_sm);
     p.n_tiles = (N + p.PT - 1) / p.PT;
     long long grid = (long long)dev.sms * occ;
@@ -466,6 +487,7 @@ int run_pair(int mode, const float* X, const float* S, int noise, int64_t N, int
         p.n_s = noise_floats_per_point(D, noise);
         p.off_X = SL.off_X; p.off_g = SL.off_g; p.stage_bytes = SL.bytes;
         p.rounds = plan.PT / plan.NSLOT;
+        p.tmem_cols = plan.tmem_cols;
     }
     void* args[] = {&p};
     const int tslot = timing_begin(st);
@@ -575,8 +597,8 @@ int dgmm_estep_stats_f32(const float* X, const float* S, int noise_layout, int64
     if (rc) return rc;
     const int total = K * (1 + D + D * D) + 1;
     finalize_stats_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
-                                                               plan.GS, plan.accp == ST_GLOBAL ? plan.TPB : plan.GS,
-                                                               plan.accp == ST_GLOBAL ? plan.NSLOT : 1, out_stats, 0);
+                                                               plan.GS, (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.TPB : plan.GS,
+                                                               (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.NSLOT : 1, out_stats, 0);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -775,8 +797,8 @@ static int stats_pass_host(dgmm_ctx* c, const float* X, const float* S, int layo
         if (r) return r;
         const int total = K * (1 + D + D * D) + 1;
         finalize_stats_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
-                                                                   plan.GS, plan.accp == ST_GLOBAL ? plan.TPB : plan.GS,
-                                                                   plan.accp == ST_GLOBAL ? plan.NSLOT : 1, c->d_stats, 1);
+                                                                   plan.GS, (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.TPB : plan.GS,
+                                                                   (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.NSLOT : 1, c->d_stats, 1);
         return (int)cudaGetLastError();
     });
 }

@@ -34,7 +34,7 @@
 namespace dgmm {
 
 enum : int { MODE_LOGLIK = 0, MODE_STATS = 1 };
-enum : int { ST_REG = 0, ST_SMEM = 1, ST_GLOBAL = 2 };  // where Sigma_j / accumulators live
+enum : int { ST_REG = 0, ST_SMEM = 1, ST_GLOBAL = 2, ST_TMEM = 3 };  // where Sigma_j / accumulators live
 enum : int { NOISE_FULL = 0, NOISE_DIAG = 1, NOISE_NONE = 2, NOISE_SHARED = 3 };
 
 constexpr int kMaxStages = 4;
@@ -62,6 +62,7 @@ struct PairParams {
     int off_X, off_g; // byte offsets of the X and g sub-tiles inside a stage (S sits at 0)
     int stage_bytes;
     int rounds;       // PT / NSLOT
+    int tmem_cols;    // columns to allocate for ST_TMEM accumulators (power of two, 32..512)
 };
 
 // ---------------------------------------------------------------------------------------
@@ -107,6 +108,43 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
+
+// ---------------------------------------------------------------------------------------
+// Tensor memory as a per-thread scratchpad (accumulator placement ST_TMEM).
+// With the 32x32b access shape lane i of warp w owns TMEM lane 32*(w % 4) + i, so every thread has
+// a private row of up to 512 fp32 columns that costs neither registers nor shared memory; the
+// K x (1 + D + D(D+1)/2) statistics live there and are updated with tcgen05.ld / tcgen05.st
+// (8 columns per instruction).  Measured (tools/ubench_tmem.cu): 150-300 B/cycle/SM of
+// read-modify-write, next to the 128 B/cycle of shared memory that the Sigma_j / S_i reads keep.
+// ---------------------------------------------------------------------------------------
+__host__ __device__ constexpr int tmem_cols_per_thread(int ns) { return (ns + 7) & ~7; }
+__host__ __device__ constexpr int tmem_alloc_cols(int ns, int warps) {
+    const int need = tmem_cols_per_thread(ns) * ((warps + 3) / 4);
+    int c = 32;
+    while (c < need) c <<= 1;
+    return c;  // > 512: does not fit
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot_in_smem, int cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_in_smem)), "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t base, int cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(base), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tmem_fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float* v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "f"(v[0]),
+                 "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]));
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // group classes of the pair kernel (see dgmm_pair_body.inc)
 enum : int { GCLS_SUB = 0, GCLS_WARP = 1, GCLS_MW4 = 2, GCLS_MWN = 3, GCLS_ANY = 4 };

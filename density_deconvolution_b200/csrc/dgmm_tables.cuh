@@ -52,11 +52,13 @@ inline PairVariant pair_by_gcls(int gcls, int nz) {
     return pair_by_gcls_nz<D, MODE, SIGP, ACCP, NZ_DIAG, MAXT, MINB>(gcls);
 }
 
-// Placements (measured on B200, profiles/):
-//   D <= 12      : Sigma_j in shared-memory columns, accumulators in registers;
-//                  STATS 128 threads x 3 blocks/SM (168 registers), LOGLIK x 4 blocks/SM (128)
-//   13 <= D <= 16: accumulators in shared-memory columns, Sigma_j from global/L1 (STATS) or shared
-//                  (LOGLIK), 255 registers
+// Placements (measured on B200, profiles/r01_placement_ab.txt; fraction of the FP32 peak, STATS):
+//   D <= 10      : Sigma_j in shared-memory columns, accumulators in registers, 128 threads x 3
+//                  blocks/SM (168 registers)                       [D=10,K=64: 0.57 vs 0.55 TMEM]
+//   D = 11, 12   : accumulators in tensor memory, 4 resp. 3 blocks/SM  [D=12: 0.59 vs 0.50 registers]
+//   13 <= D <= 16: Sigma_j in shared-memory columns, accumulators in tensor memory, 255 registers,
+//                  2 blocks/SM       [D=16,K=128: 0.61 vs 0.44 with shared-memory accumulators]
+//   LOGLIK       : Sigma_j in shared-memory columns; 128 registers x 4 blocks/SM (D <= 12), 255 above
 //   D > 16       : fallback only (rolled loops, local-memory arrays)
 template <int D>
 inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
@@ -66,11 +68,19 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
         return pair_variant<D, MODE_STATS, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
     }
     if (which != 0) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};  // no alternative placements compiled
+    // Accumulators in tensor memory need warp-uniform control flow: sub-warp groups (K < 32) keep
+    // the register / shared-memory placements.
     if constexpr (D <= 12) {
         if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 4>(gcls, nz);
+        if constexpr (D == 11) {
+            if (gcls != GCLS_SUB) return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_TMEM, 128, 4>(gcls, nz);
+        } else if constexpr (D == 12) {
+            if (gcls != GCLS_SUB) return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_TMEM, 128, 3>(gcls, nz);
+        }
         return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_REG, 128, 3>(gcls, nz);
     } else if constexpr (D <= DGMM_UNROLL_D) {
         if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, kPairMaxThreads, 1>(gcls, nz);
+        if (gcls != GCLS_SUB) return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_TMEM, kPairMaxThreads, 1>(gcls, nz);
         return pair_by_gcls<D, MODE_STATS, ST_GLOBAL, ST_SMEM, kPairMaxThreads, 1>(gcls, nz);
     }
     return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
