@@ -25,6 +25,7 @@ SYMBOLS = (
     "dgmm_abi_version", "dgmm_supported_dims", "dgmm_workspace_bytes", "dgmm_loglik_f32",
     "dgmm_estep_stats_f32", "dgmm_estep_full_f32", "dgmm_mstep_update_f32", "dgmm_fp32_probe",
     "dgmm_ctx_create", "dgmm_ctx_destroy", "dgmm_em_iteration_host", "dgmm_estep_stats_host", "dgmm_score_host",
+    "dgmm_kmeans_workspace_bytes", "dgmm_kmeans_assign_f32", "dgmm_kmeans_update_f32",
     "dgmm_debug_set_tuning", "dgmm_debug_get_plan", "dgmm_debug_pair_timing", "dgmm_debug_pair_times",
 )
 
@@ -88,6 +89,12 @@ def lib():
     L.dgmm_estep_stats_host.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp, f32, vp]
     L.dgmm_score_host.restype = i32
     L.dgmm_score_host.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp, vp, ctypes.POINTER(f64), ctypes.POINTER(i64)]
+    L.dgmm_kmeans_workspace_bytes.restype = sz
+    L.dgmm_kmeans_workspace_bytes.argtypes = [i32, i32]
+    L.dgmm_kmeans_assign_f32.restype = i32
+    L.dgmm_kmeans_assign_f32.argtypes = [vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
+    L.dgmm_kmeans_update_f32.restype = i32
+    L.dgmm_kmeans_update_f32.argtypes = [i32, vp, i32, i32, vp, vp, vp]
     L.dgmm_debug_set_tuning.restype = i32
     L.dgmm_debug_set_tuning.argtypes = [i32] * 8
     L.dgmm_debug_get_plan.restype = i32

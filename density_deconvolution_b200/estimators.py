@@ -122,7 +122,7 @@ class DeconvGMM:
 
     # -- initialisation (deconv_gmm.py:21-34 + the first _m_step of base.py:41-42) -----------
     def _kmeans_init(self, X, max_iters=50, tol=1e-9):
-        return k_means(X, self.k, max_iters, tol, self.device)[0]
+        return k_means(X, self.k, max_iters, tol, self.device, ops=_ops)[0]
 
     def _init_expectations(self, data):
         X, _, _ = self._prep(data)
@@ -161,7 +161,7 @@ class DeconvGMM:
         X, S, layout = self._prep(data)
         n_total = _global_count(X.shape[0], self.device)
         if init:
-            resps, centroids = k_means(X, self.k, 50, 1e-9, self.device)
+            resps, centroids = k_means(X, self.k, 50, 1e-9, self.device, ops=_ops)
             self._init_from_labels(X, resps, centroids)
         mix = self._mixture()
         stats = torch.empty(_ops.stats_len(self.d, self.k), dtype=torch.float32, device=self.device)
@@ -264,7 +264,7 @@ class OnlineDeconvGMM(DeconvGMM):
 
     def _init_sum_stats(self, loader, n):
         """online_deconv_gmm.py:26-40: minibatch k-means -> weights/means, identity covariances."""
-        counts, centroids = minibatch_k_means(loader, self.k, max_iters=self.k_means_iters, device=self.device)
+        counts, centroids = minibatch_k_means(loader, self.k, max_iters=self.k_means_iters, device=self.device, ops=_ops)
         self.set_params(counts[:, None] / counts.sum(), centroids,
                         torch.eye(self.d, device=self.device).repeat(self.k, 1, 1))
         self._reset_running_sums()
@@ -590,7 +590,7 @@ class BaseSGDGMM:
 
     def init_params(self, loader):
         """sgd_gmm.py:256-261."""
-        counts, centroids = minibatch_k_means(loader, self.k, max_iters=self.k_means_iters, device=self.device)
+        counts, centroids = minibatch_k_means(loader, self.k, max_iters=self.k_means_iters, device=self.device, ops=_ops)
         with torch.no_grad():
             self.module.soft_weights.copy_(torch.log(counts / counts.sum()))
             self.module.means.copy_(centroids)

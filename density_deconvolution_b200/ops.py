@@ -277,3 +277,65 @@ class HostContext:
             self._host(ll, "out_ll") if want_ll else ctypes.c_void_p(0), ctypes.byref(tot), ctypes.byref(bad)),
             "dgmm_score_host")
         return (tot.value, bad.value, ll) if want_ll else (tot.value, bad.value)
+
+
+# -----------------------------------------------------------------------------------------
+# initialisation: fused k-means assignment
+# -----------------------------------------------------------------------------------------
+_km_workspaces = {}
+
+
+def kmeans_stats_len(D, K):
+    return K * (1 + D) + 2
+
+
+def _km_workspace(D, K, device):
+    key = (D, K, device.index if device.index is not None else torch.cuda.current_device())
+    ws = _km_workspaces.get(key)
+    if ws is None:
+        with torch.cuda.device(device):
+            nbytes = _lib.lib().dgmm_kmeans_workspace_bytes(D, K)
+        if nbytes == 0:
+            raise DgmmError("dgmm_kmeans_workspace_bytes(D=%d, K=%d) failed" % (D, K))
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _km_workspaces[key] = ws
+    return ws
+
+
+def kmeans_assign(X, centroids, want_labels=False, out_stats=None):
+    """Nearest-centroid labels and, in the same pass, the packed ``[counts K | sums K*D | dist_hi |
+    dist_lo]`` buffer (deconv/gmm/util.py:19-24,51-64).  Returns ``(labels int32 [N] or None, stats)``."""
+    X = _f32c(X, "X")
+    dev = X.device
+    centroids = _f32c(centroids, "centroids", dev)
+    N, D = X.shape
+    K = centroids.shape[0]
+    if centroids.shape[1] != D:
+        raise ValueError("centroids %s do not match X %s" % (tuple(centroids.shape), tuple(X.shape)))
+    labels = torch.empty(N, dtype=torch.int32, device=dev) if want_labels else None
+    stats = out_stats if out_stats is not None else torch.empty(kmeans_stats_len(D, K), dtype=torch.float32, device=dev)
+    ws = _km_workspace(D, K, dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_kmeans_assign_f32(_ptr(X), N, D, K, _ptr(centroids), _ptr(labels), _ptr(stats), _ptr(ws),
+                                               ws.numel(), _stream(dev))
+    check(rc, "dgmm_kmeans_assign_f32")
+    return labels, stats
+
+
+def kmeans_update(mode, stats, centroids, counts_run=None):
+    """In-place centroid update from the (all-reduced) packed buffer: ``mode='lloyd'`` or
+    ``'minibatch'`` (the latter also advances ``counts_run [K]``)."""
+    dev = stats.device
+    K, D = centroids.shape
+    for name, t in (("stats", stats), ("centroids", centroids), ("counts_run", counts_run)):
+        if t is not None and not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise DgmmError("%s must be a contiguous float32 CUDA tensor (updated in place)" % name)
+    code = {"lloyd": 0, "minibatch": 1}[mode]
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_kmeans_update_f32(code, _ptr(stats), D, K, _ptr(centroids), _ptr(counts_run), _stream(dev))
+    check(rc, "dgmm_kmeans_update_f32")
+
+
+def kmeans_total_distance(stats):
+    """``sum_i min_j |x_i - c_j|`` from the packed buffer (a float pair carrying a double)."""
+    return float(stats[-2].item()) + float(stats[-1].item())

@@ -1,8 +1,13 @@
-"""Initialisation helpers (reference: deconv/gmm/util.py).  Not on the hot path: plain
-torch ops on the device, written without the reference's ``[B,K,D]`` mask tensors.  Under
-``torch.distributed`` every rank passes its own shard and the counts / sums are all-reduced,
-so all ranks end with identical centroids (ranks must make the same number of batches)."""
+"""Initialisation helpers (reference: deconv/gmm/util.py) on the fused k-means kernel
+(``dgmm_kmeans_assign_f32`` / ``dgmm_kmeans_update_f32``): one pass over the
+points yields labels, per-centroid counts, coordinate sums and the total distance, so neither the
+reference's ``[B,K,D]`` difference / mask tensors nor its Python loop over centroids exist here.
+Under ``torch.distributed`` every rank passes its own shard and the packed ``K(1+D)+2`` floats are
+all-reduced, so all ranks end with identical centroids (ranks must make the same number of
+batches).  There is no torch fallback: the tensors must live on the GPU."""
 import torch
+
+from . import ops as _real_ops
 
 from . import dist as _dist
 
@@ -21,49 +26,49 @@ def _from_rank0(t):
     return t
 
 
-def k_means(X, k, max_iters=50, tol=1e-9, device=None, generator=None):
+def k_means(X, k, max_iters=50, tol=1e-9, device=None, generator=None, ops=None):
     """Lloyd's k-means from uniformly drawn centroids in the bounding box
     (deconv/gmm/util.py:4-33).  Returns ``(one-hot resp [N,k] float, centroids [k,D])``.
     Deliberate fix: an empty cluster keeps its previous centroid
     instead of becoming NaN (util.py:24), which made ``DeconvGMM.fit`` fail at iteration 0."""
+    ops = ops or _real_ops
     n, d = X.shape
     lo = _allreduce(X.min(dim=0)[0], "min")
     hi = _allreduce(X.max(dim=0)[0], "max")
-    centroids = _from_rank0(torch.rand(k, d, device=X.device, generator=generator)) * (hi - lo) + lo
+    centroids = (_from_rank0(torch.rand(k, d, device=X.device, generator=generator)) * (hi - lo) + lo).contiguous()
     prev = None
     for _ in range(max_iters):
-        dist = torch.cdist(X, centroids)
-        labels = dist.argmin(dim=1)
-        counts = _allreduce(torch.bincount(labels, minlength=k).to(X.dtype))
-        sums = _allreduce(torch.zeros(k, d, device=X.device, dtype=X.dtype).index_add_(0, labels, X))
-        centroids = torch.where(counts[:, None] > 0, sums / counts.clamp(min=1)[:, None], centroids)
-        total = _allreduce(dist.gather(1, labels[:, None]).sum())
-        if prev is not None and torch.abs(total - prev) < tol:
+        # labels and distances are taken against the centroids the pass started from (util.py:20-21)
+        labels, stats = ops.kmeans_assign(X, centroids, want_labels=True)
+        _allreduce(stats)
+        ops.kmeans_update("lloyd", stats, centroids)
+        total = ops.kmeans_total_distance(stats)
+        if prev is not None and abs(total - prev) < tol:
             break
         prev = total
     resp = torch.zeros(n, k, device=X.device, dtype=X.dtype)
-    resp[torch.arange(n, device=X.device), labels] = 1.0
+    resp[torch.arange(n, device=X.device), labels.long()] = 1.0
     return resp, centroids
 
 
-def minibatch_k_means(loader, k, max_iters=50, tol=1e-3, device=None):
+def minibatch_k_means(loader, k, max_iters=50, tol=1e-3, device=None, ops=None):
     """Sculley's minibatch k-means with per-centre learning rates ``1/count``
     (deconv/gmm/util.py:36-75).  ``loader`` yields ``(X_b, ...)`` batches.  Returns
     ``(counts [k], centroids [k,D])``."""
+    ops = ops or _real_ops
     first = next(iter(loader))[0]
-    centroids = _from_rank0(first[:k].to(device).clone())
+    centroids = _from_rank0(first[:k].to(device=device, dtype=torch.float32).clone()).contiguous()
     counts = torch.ones(k, device=centroids.device)
     prev_norm = torch.tensor(0.0, device=centroids.device)
+    stats = None
     for _ in range(max_iters):
         for batch in loader:
             X = batch[0].to(centroids.device)
-            labels = torch.cdist(X, centroids).argmin(dim=1)
-            counts = counts + _allreduce(torch.bincount(labels, minlength=k).to(counts.dtype))
-            eta = 1.0 / counts
-            # sum over the batch of eta_c (x - centroid_c) for the points assigned to c,
-            # all taken against the centroids at the start of the batch as in the reference
-            shift = _allreduce(torch.zeros_like(centroids).index_add_(0, labels, X - centroids[labels]))
-            centroids = centroids + eta[:, None] * shift
+            # counts and the shift sum_i (x_i - c_label) are both taken against the centroids at the
+            # start of the batch, as in the reference (util.py:53-64)
+            _, stats = ops.kmeans_assign(X, centroids, out_stats=stats)
+            _allreduce(stats)
+            ops.kmeans_update("minibatch", stats, centroids, counts)
         norm = torch.norm(centroids, dim=0).sum()
         if torch.abs(norm - prev_norm) < tol:
             break

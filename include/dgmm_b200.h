@@ -165,6 +165,39 @@ DGMM_API int dgmm_score_host(dgmm_ctx* ctx, const float* X, const float* S, int 
                     const float* alpha, const float* mu, const float* Sigma,
                     float* out_ll, double* ll_sum, int64_t* nonpd);
 
+/* ---- initialisation: fused k-means assignment (device pointers) ----------------------- */
+
+/* Packed buffer written by dgmm_kmeans_assign_f32:
+ *   [ counts (K) | sums (K*D) | dist_hi | dist_lo ]
+ * counts_j = #{i : label_i = j}, sums_j = sum of the x_i assigned to j, dist_hi + dist_lo =
+ * sum_i min_j |x_i - c_j| (Euclidean norm; a float pair carrying a double).  Every slot is additive
+ * across shards: one all-reduce(SUM) of K*(1+D)+2 floats per k-means pass. */
+static inline size_t dgmm_kmeans_stats_len(int D, int K) {
+    return (size_t)K * (size_t)(1 + D) + 2;
+}
+
+/* Bytes of device workspace needed by dgmm_kmeans_assign_f32 (0 on error). */
+DGMM_API size_t dgmm_kmeans_workspace_bytes(int D, int K);
+
+/* Nearest-centroid assignment of X [N,D] against centroids [K,D] and, in the same pass, the
+ * per-centroid counts and coordinate sums (ties -> lowest index, as torch.min).  Replaces the
+ * [B,K,D] difference tensor, argmin, bincount and mask reduction of
+ * deconv/gmm/util.py:19-24 (k_means) and deconv/gmm/util.py:51-64 (minibatch_k_means).
+ *   labels (optional) [N] int32; out_stats [dgmm_kmeans_stats_len(D,K)].
+ * Deterministic (no atomics; fixed summation order for a given N and device). */
+DGMM_API int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, const float* centroids,
+                                    int32_t* labels, float* out_stats, void* workspace, size_t workspace_bytes,
+                                    void* stream);
+
+/* Centroid update from the (all-reduced) packed buffer, in place.
+ *   mode 0, Lloyd (deconv/gmm/util.py:23-24): c_j = sums_j / counts_j; an empty cluster keeps its
+ *           centroid (the reference writes NaN there: documented fix).
+ *   mode 1, minibatch (deconv/gmm/util.py:56-64): counts_run_j += counts_j;
+ *           c_j += (sums_j - counts_j c_j) / counts_run_j   (per-centre rate 1/count).
+ * counts_run [K] is read and written for mode 1 only. */
+DGMM_API int dgmm_kmeans_update_f32(int mode, const float* stats, int D, int K, float* centroids,
+                                    float* counts_run, void* stream);
+
 /* ---- diagnostics (not part of the drop-in surface) ----------------------------------- */
 
 /* Overrides the automatic launch plan of the pair kernel; -1 = automatic for that field.

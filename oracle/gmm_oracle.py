@@ -302,3 +302,40 @@ def sgd_reg_loss(l_diag, l_lower, means, n, n_total, w, dtype=np.float64):
     _, _, Sigma, _ = sgd_to_mixture(np.zeros(K), means, l_diag, l_lower, dtype)
     diag = np.diagonal(Sigma, axis1=-2, axis2=-1)
     return float(((n / n_total) * w / diag).sum())
+
+
+# ---------------------------------------------------------------------------------------------
+# k-means initialisation (deconv/gmm/util.py)
+# ---------------------------------------------------------------------------------------------
+def kmeans_assign(X, centroids, dtype=np.float64):
+    """Labels, counts, coordinate sums and total distance of one assignment pass.
+    deconv/gmm/util.py:19-20 / :51-52 (``diffs.norm(dim=2).min(dim=1)[1]``; ties -> lowest index),
+    :54 (bincount), :22-24 / :59-64 (the per-label sums behind the cluster means / masked shift),
+    :27 (``distances[resp].sum()``)."""
+    X = np.asarray(X, dtype=dtype)
+    C = np.asarray(centroids, dtype=dtype)
+    K = C.shape[0]
+    dist = np.sqrt(((X[:, None, :] - C[None, :, :]) ** 2).sum(axis=2)) if len(X) else np.zeros((0, K), dtype=dtype)
+    labels = dist.argmin(axis=1) if len(X) else np.zeros(0, dtype=np.int64)
+    counts = np.bincount(labels, minlength=K).astype(dtype)
+    sums = np.zeros_like(C)
+    np.add.at(sums, labels, X)
+    total = float(dist[np.arange(len(X)), labels].sum()) if len(X) else 0.0
+    return labels, counts, sums, total
+
+
+def kmeans_lloyd_update(counts, sums, centroids):
+    """deconv/gmm/util.py:22-24 (cluster means); an empty cluster keeps its centroid (documented fix:
+    the reference writes NaN there)."""
+    C = np.array(centroids, dtype=np.float64)
+    nz = counts > 0
+    C[nz] = sums[nz] / counts[nz][:, None]
+    return C
+
+
+def kmeans_minibatch_update(counts, sums, centroids, counts_run):
+    """deconv/gmm/util.py:54-64: ``counts += bincount``, ``eta = 1/counts``,
+    ``centroids += sum_i eta_c (x_i - c)`` over the points assigned to c."""
+    n_new = np.asarray(counts_run, dtype=np.float64) + counts
+    C = np.asarray(centroids, dtype=np.float64)
+    return C + (sums - counts[:, None] * C) / n_new[:, None], n_new

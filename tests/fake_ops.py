@@ -106,3 +106,37 @@ def mstep_update(stats, n_total, w, mu, Sigma, alpha, log_alpha):
     Sigma.copy_(torch.tensor(covars, dtype=torch.float32))
     alpha.copy_(torch.tensor(wts[:, 0], dtype=torch.float32))
     log_alpha.copy_(torch.log(alpha))
+
+
+# ---- k-means (ops.kmeans_*) ------------------------------------------------------------------
+def kmeans_stats_len(D, K):
+    return K * (1 + D) + 2
+
+
+def kmeans_assign(X, centroids, want_labels=False, out_stats=None):
+    K, D = centroids.shape
+    labels, counts, sums, total = orc.kmeans_assign(_np(X), _np(centroids))
+    hi = np.float32(total)
+    buf = np.concatenate([counts, sums.reshape(-1), [float(hi), total - float(hi)]])
+    stats = torch.tensor(buf, dtype=torch.float32, device=X.device)
+    if out_stats is not None:
+        out_stats.copy_(stats)
+        stats = out_stats
+    lab = torch.tensor(labels, dtype=torch.int32, device=X.device) if want_labels else None
+    return lab, stats
+
+
+def kmeans_update(mode, stats, centroids, counts_run=None):
+    K, D = centroids.shape
+    s = _np(stats)
+    counts, sums = s[:K], s[K:K + K * D].reshape(K, D)
+    if mode == "lloyd":
+        new = orc.kmeans_lloyd_update(counts, sums, _np(centroids))
+    else:
+        new, n_new = orc.kmeans_minibatch_update(counts, sums, _np(centroids), _np(counts_run))
+        counts_run.copy_(torch.tensor(n_new, dtype=torch.float32))
+    centroids.copy_(torch.tensor(new, dtype=torch.float32))
+
+
+def kmeans_total_distance(stats):
+    return float(stats[-2].item()) + float(stats[-1].item())

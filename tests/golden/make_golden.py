@@ -252,7 +252,55 @@ def boston_case(name):
     print(name, lls[0], lls[-1])
 
 
+def kmeans_case(name):
+    """deconv/gmm/util.py: ``minibatch_k_means`` over a list-of-batches loader and ``k_means`` (its
+    ``torch.rand`` initial centroids are re-drawn here from the same seed), float32 and float64."""
+    import contextlib
+    import io
+    from deconv.gmm.util import k_means, minibatch_k_means
+    rng = np.random.default_rng(777)
+    out = {}
+    for tag, dtype, N, D, K in (("f64", torch.float64, 240, 3, 4), ("f32", torch.float32, 300, 5, 6)):
+        centres = rng.normal(size=(K, D)) * 4.0
+        X = torch.tensor(centres[rng.integers(0, K, N)] + rng.normal(size=(N, D)), dtype=dtype)
+        old = torch.get_default_dtype()
+        torch.set_default_dtype(dtype)
+
+        class Loader:     # fresh batch tensors per pass, like a DataLoader (the reference's centroids
+            def __iter__(self):  # are a view of the first batch and are updated in place)
+                return iter([(X[lo:lo + 60].clone(),) for lo in range(0, N, 60)])
+        batches = Loader()
+        for iters in (1, 3):
+            with contextlib.redirect_stdout(io.StringIO()):
+                counts, cents = minibatch_k_means(batches, K, max_iters=iters, tol=0.0)
+            out["mb_%s_counts_%d" % (tag, iters)] = counts.numpy().copy()
+            out["mb_%s_centroids_%d" % (tag, iters)] = cents.numpy().copy()
+        for seed in range(1000):          # the reference turns an empty cluster into NaN: find a seed without one
+            torch.manual_seed(seed)
+            with contextlib.redirect_stdout(io.StringIO()):
+                if not torch.isnan(k_means(X, K, max_iters=4, tol=0.0)[1]).any():
+                    break
+        else:
+            raise RuntimeError("no seed without an empty cluster")
+        torch.manual_seed(seed)
+        init = torch.rand(K, D) * (X.max(dim=0)[0] - X.min(dim=0)[0]) + X.min(dim=0)[0]
+        for iters in (1, 4):
+            torch.manual_seed(seed)
+            resp, cents = k_means(X, K, max_iters=iters, tol=0.0)
+            assert not torch.isnan(cents).any()
+            out["ll_%s_resp_%d" % (tag, iters)] = resp.numpy().copy()
+            out["ll_%s_centroids_%d" % (tag, iters)] = cents.numpy().copy()
+        out["ll_%s_init" % tag] = init.numpy().copy()
+        out["X_%s" % tag] = X.numpy().copy()
+        torch.set_default_dtype(old)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, sorted(out))
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "kmeans":
+        kmeans_case("ref_kmeans.npz")
+        return
     rng = np.random.default_rng(12345)
     em_case("ref_em_d3_k4_f64.npz", rng, N=40, D=3, K=4, dtype=torch.float64)
     em_case("ref_em_d10_k6_f64.npz", rng, N=24, D=10, K=6, dtype=torch.float64)
@@ -265,6 +313,7 @@ def main():
     data_gen_case("ref_data_gen.npz")
     robustness_case("ref_robust_f32.npz")
     boston_case("ref_boston_k10_f64.npz")
+    kmeans_case("ref_kmeans.npz")
 
 
 if __name__ == "__main__":
