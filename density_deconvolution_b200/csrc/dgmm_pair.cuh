@@ -171,6 +171,14 @@ __device__ __forceinline__ float warp_max_f32(float v) {
     return r;
 }
 
+// Lanes that share one point in the per-tile logsumexp pass of the log-likelihood kernel: the
+// largest power of two <= min(32, TPB / PT).
+__host__ __device__ inline int lse_lanes(int TPB, int PT) {
+    int r = 1;
+    while (2 * r <= 32 && 2 * r * PT <= TPB) r <<= 1;
+    return r;
+}
+
 // Bytes of one ring stage and the offsets of its three sub-tiles (all multiples of 16).
 __host__ __device__ inline int noise_floats_per_point(int D, int noise) {
     return noise == NOISE_FULL ? D * D : (noise == NOISE_DIAG ? D : 0);

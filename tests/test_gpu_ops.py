@@ -47,7 +47,10 @@ def run_case(ops, N, D, K, seed, noise="full", with_g=False, floor=0.0):
     assert np.all(np.isfinite(ll_d))
     assert abs(ll_d.mean() - ll.mean()) <= LL_RTOL * abs(ll.mean())
     assert np.max(np.abs(ll_d - ll)) <= 2e-4 * max(1.0, np.max(np.abs(ll)))
-    assert np.array_equal(ll2_d.cpu().numpy(), ll_d.astype(np.float32)), "stats pass and loglik pass disagree"
+    # the two passes sum the K densities in different orders (warp butterflies vs the per-tile pass of
+    # the log-likelihood kernel): equal to float32 rounding of the logsumexp, not bit for bit
+    np.testing.assert_allclose(ll2_d.cpu().numpy(), ll_d.astype(np.float32), rtol=2e-6, atol=2e-6,
+                               err_msg="stats pass and loglik pass disagree")
     assert abs(sums[0].item() - ll.sum()) <= LL_RTOL * abs(ll.sum())
     assert sums[1].item() == 0
     d0, d1, d2, tail = [t.cpu().numpy().astype(np.float64) for t in ops.unpack_stats(stats, D, K)]
@@ -279,7 +282,9 @@ def test_large_n_properties(ops):
     assert abs((tot[-4] + tot[-3]) - (ref[-4] + ref[-3])) < 1e-6 * abs(ref[-4].item())
     s0 = ref[:K]
     assert abs(s0.sum().item() - N) < 1e-4 * N          # responsibilities sum to one per point
-    assert torch.equal(ops.loglik(X, S, la, mu, Sigma), ll)
+    ll_pass = ops.loglik(X, S, la, mu, Sigma)
+    assert torch.equal(ops.loglik(X, S, la, mu, Sigma), ll_pass), "log-likelihood pass is deterministic"
+    assert torch.allclose(ll_pass, ll, rtol=2e-6, atol=2e-6)   # different summation order of the K densities
     # oracle on a slice
     idx = slice(1000, 1256)
     want = orc.loglik(X[idx].cpu().numpy(), S[idx].cpu().numpy(), alpha.cpu().numpy(), mu.cpu().numpy(),

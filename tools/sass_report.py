@@ -59,7 +59,8 @@ def main():
                 if t and int(t.group(1), 16) < addr:
                     tgt = int(t.group(1), 16)
                     body = [o for a, o, _ in ins if tgt <= a <= addr]
-                    if any(o.startswith("MUFU.RCP") or o.startswith("MUFU.RSQ") for o in body):
+                    if sum(o.startswith("FFMA") for o in body) >= 20 and \
+                            any(o.startswith("MUFU.RCP") or o.startswith("MUFU.RSQ") for o in body):
                         if best is None or len(body) < len(best):
                             best = body
         if best:
