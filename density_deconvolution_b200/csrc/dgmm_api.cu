@@ -304,7 +304,7 @@ size_t pair_smem_bytes(int D, int noise, bool has_g, int sigp, int accp, int GS,
     size_t b = kSmemHeader + (size_t)NST * SL.bytes;
     if (sigp == ST_SMEM) b += (size_t)pad_col(nd_of(D)) * GS * 4;
     if (mode == MODE_STATS && accp == ST_SMEM) b += (size_t)pad_col(ns_of(D)) * TPB * 4;
-    if (mode == MODE_LOGLIK) b += (size_t)2 * PT * (GS + lse_lanes(TPB, PT)) * 4;  // deferred logsumexp rows
+    if (mode == MODE_LOGLIK) b += (size_t)2 * PT * (GS + 16) * 4;  // deferred logsumexp rows
     // the register-accumulator epilogue reuses the ring as TPB floats of scratch
     if (b < kSmemHeader + (size_t)TPB * 4) b = kSmemHeader + (size_t)TPB * 4;
     return b;

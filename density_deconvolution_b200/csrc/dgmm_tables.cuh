@@ -67,11 +67,17 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
             return pair_variant<D, MODE_LOGLIK, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
         return pair_variant<D, MODE_STATS, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
     }
-    if (which != 0) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};  // no alternative placements compiled
+    if (which == 1) {  // alternative placements (tuning sweeps, tools/gpu_ab.sh)
+        if constexpr (D <= 12) {
+            if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 4>(gcls, nz);
+        }
+        return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
+    }
+    if (which != 0) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
     // Accumulators in tensor memory need warp-uniform control flow: sub-warp groups (K < 32) keep
     // the register / shared-memory placements.
     if constexpr (D <= 12) {
-        if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 4>(gcls, nz);
+        if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 3>(gcls, nz);
         if constexpr (D == 11) {
             if (gcls != GCLS_SUB) return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_TMEM, 128, 4>(gcls, nz);
         } else if constexpr (D == 12) {

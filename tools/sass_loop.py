@@ -19,7 +19,7 @@ for f in re.split(r"\n\s*Function : ", txt)[1:]:
         if m and int(m.group(2), 16) < addr:
             tgt = int(m.group(2), 16)
             body = [(a, x) for a, x in ins if tgt <= a <= addr]
-            if any("MUFU.RCP" in x or "MUFU.RSQ" in x for _, x in body):
+            if sum("FFMA" in x for _, x in body) >= 20 and any("MUFU.RCP" in x or "MUFU.RSQ" in x for _, x in body):
                 if best is None or len(body) < len(best): best = body
     for a, x in best:
         if nofp and re.match(r"(@!?P\d+\s+)?(FFMA|FMUL|FADD)\b", x): continue
