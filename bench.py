@@ -61,6 +61,8 @@ def parse_args():
     ap.add_argument("--points", type=int, default=0, help="override points per GPU")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-sgd", action="store_true")
+    ap.add_argument("--sgd-batch", type=int, default=65536, help="SGD minibatch per GPU")
     return ap.parse_args()
 
 
@@ -288,6 +290,11 @@ def run_b200(args, wl):
     pair_ms_ll = ops.pair_times()
     ops.pair_timing(False)
 
+    # ---- minibatch SGD steps through the estimator API (configs[4]: Adam, lr 1e-3, w 1e-3) --------
+    sgd = None
+    if not args.no_sgd:
+        sgd = run_sgd(args, wl, dev, world, X, S, fresh, barrier)
+
     if sampler:
         time.sleep(0.06)
         sampler.stop()
@@ -346,12 +353,56 @@ def run_b200(args, wl):
         mean_loglik_after=ll_after, nonpd_pairs=nonpd,
         gpu_launches=4 * args.steps,
         gpu_launches_note="per step: prepare_kernel, pair_kernel<STATS>, finalize_stats_kernel, mstep_kernel",
-        clocks=clocks, roofline=roofline, e2e=e2e)
+        sgd=sgd, clocks=clocks, roofline=roofline, e2e=e2e)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(wl)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_sgd(args, wl, dev, world, X, S, fresh, barrier, n_steps=20):
+    """Minibatch-SGD steps (forward + backward in ONE fused statistics launch, stats all-reduce,
+    Adam on the [K,.] parameters) through ``SGDDeconvGMM.fit`` on a resident slice of the shard:
+    ``n_steps`` minibatches of ``--sgd-batch`` points per GPU, one epoch, device-side shuffling."""
+    import torch
+    from density_deconvolution_b200.estimators import SGDDeconvGMM
+    N, D = X.shape
+    K = wl["K"]
+    B = min(args.sgd_batch, N)
+    n_steps = max(1, min(n_steps, N // B))
+    n_sub = n_steps * B
+    a, _, m, Sg = fresh()
+
+    def make():
+        est = SGDDeconvGMM(K, D, epochs=1, lr=1e-3, batch_size=B, w=1e-3, device=dev)
+        with torch.no_grad():
+            est.module.soft_weights.copy_(a.log())
+            est.module.means.copy_(m)
+            L = torch.linalg.cholesky(Sg.double()).float()
+            est.module.l_diag.copy_(torch.diagonal(L, dim1=1, dim2=2).log())
+            idx = est.module.l_idx
+            est.module.l_lower.copy_(L[:, idx[0], idx[1]])
+        return est
+
+    make().fit((X[:min(3 * B, n_sub)], S[:min(3 * B, n_sub)]), init=False)       # warm-up (3 steps)
+    est = make()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    est.fit((X[:n_sub], S[:n_sub]), init=False)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    barrier()
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    t = ms.item() * 1e-3
+    return dict(api="SGDDeconvGMM.fit (1 epoch, device-resident batches, shuffle on device)",
+                batch_per_gpu=B, global_batch=B * world, steps=n_steps, ms_per_step=t / n_steps * 1e3,
+                steps_per_sec=n_steps / t, points_per_sec=float(n_sub) * world / t,
+                pair_evals_per_sec=float(n_sub) * world * K / t, mean_loglik=est.train_loss_curve[-1])
 
 
 def run_e2e(args, wl, ops, dist, dev, world, X, S, fresh, n_total, w_reg, barrier):

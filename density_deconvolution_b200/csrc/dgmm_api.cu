@@ -159,54 +159,84 @@ __global__ void prepare_kernel(const float* __restrict__ log_alpha, const float*
 
 // Sums the per-block partials (double accumulation, fixed order: deterministic) into the
 // packed statistics buffer.  beta = 1 accumulates onto the existing contents (host pipeline).
-__global__ void finalize_stats_kernel(const float* __restrict__ part, const double* __restrict__ part_ll,
-                                      const int* __restrict__ nonpd, int nblk, int D, int K, int GS, int cols,
-                                      int nslot, float* __restrict__ stats, int beta) {
+// One block per (packed statistic e, tile of 32 components): lane x -> component j (coalesced
+// 128-byte reads of the partials), the 8 warps take the (block, slot) rows r = y, y + 8, ..., and
+// their sums are combined in warp order.  The last block reduces the (sum ll, sum g) pairs.
+constexpr int kFinY = 8;
+__global__ void __launch_bounds__(32 * kFinY) finalize_stats_kernel(
+    const float* __restrict__ part, const double* __restrict__ part_ll, const int* __restrict__ nonpd, int nblk,
+    int D, int K, int GS, int cols, int nslot, float* __restrict__ stats, int beta) {
+    __shared__ double sh[2][kFinY][32];
     const int ND = D * (D + 1) / 2, NS = 1 + D + ND;
-    const int per = 1 + D + D * D;
-    const int total = K * per;
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid < total) {
-        // map output slot -> (j, packed element e)
-        int j, e, out;
-        if (tid < K) {
-            j = tid; e = 0; out = j;
-        } else if (tid < K + K * D) {
-            const int r = tid - K;
-            const int a = r / K; j = r - a * K;         // j fastest for coalesced partial reads
-            e = 1 + a; out = K + j * D + a;
-        } else {
-            const int r = tid - K - K * D;
-            const int ab = r / K; j = r - ab * K;
-            const int a = ab / D, b = ab - a * D;
-            const int hi = a > b ? a : b, lo = a > b ? b : a;
-            e = 1 + D + hi * (hi + 1) / 2 + lo;
-            out = K + K * D + (j * D + a) * D + b;
-        }
-        double s = 0.0;
+    const int njt = (K + 31) / 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int total = K * (1 + D + D * D);
+    if ((int)blockIdx.x < NS * njt) {
+        const int e = blockIdx.x / njt, j = (blockIdx.x - e * njt) * 32 + tx;
         // `cols` columns per block: GS when the block already summed its slots, TPB (= nslot * GS)
         // when the accumulators are per-thread global columns
-        for (int blk = 0; blk < nblk; ++blk)
-            for (int sl = 0; sl < nslot; ++sl) s += (double)part[((size_t)blk * NS + e) * cols + sl * GS + j];
-        stats[out] = beta ? (stats[out] + (float)s) : (float)s;
-    } else if (tid == total) {
+        const int rows = nblk * nslot;
+        double s = 0.0;
+        if (j < K) {
+#pragma unroll 4
+            for (int r = ty; r < rows; r += kFinY) {
+                const int blk = r / nslot, sl = r - blk * nslot;
+                s += (double)part[((size_t)blk * NS + e) * cols + sl * GS + j];
+            }
+        }
+        sh[0][ty][tx] = s;
+        __syncthreads();
+        if (ty == 0 && j < K) {
+            double t = 0.0;
+#pragma unroll
+            for (int y = 0; y < kFinY; ++y) t += sh[0][y][tx];
+            const float v = (float)t;
+            if (e == 0) {
+                stats[j] = beta ? stats[j] + v : v;
+            } else if (e < 1 + D) {
+                float* o = stats + K + j * D + (e - 1);
+                *o = beta ? *o + v : v;
+            } else {
+                int a = 0;
+                const int tt = e - 1 - D;
+                while ((a + 1) * (a + 2) / 2 <= tt) ++a;
+                const int b = tt - a * (a + 1) / 2;
+                float* base = stats + K + K * D + (size_t)j * D * D;
+                const float nv = beta ? base[a * D + b] + v : v;
+                base[a * D + b] = nv;
+                base[b * D + a] = nv;       // the full symmetric matrix is stored
+            }
+        }
+    } else {
+        const int t = ty * 32 + tx;
         double ll = 0.0, sg = 0.0;
-        for (int blk = 0; blk < nblk; ++blk) { ll += part_ll[2 * blk]; sg += part_ll[2 * blk + 1]; }
-        float* tail = stats + total;
-        if (beta) ll += (double)tail[0] + (double)tail[1];
-        const float hi = (float)ll;
-        tail[0] = hi;
-        tail[1] = isfinite(hi) ? (float)(ll - (double)hi) : 0.f;
-        tail[2] = beta ? tail[2] + (float)sg : (float)sg;
-        tail[3] = beta ? tail[3] + (float)(*nonpd) : (float)(*nonpd);
+        for (int blk = t; blk < nblk; blk += 32 * kFinY) { ll += part_ll[2 * blk]; sg += part_ll[2 * blk + 1]; }
+        sh[0][ty][tx] = ll;
+        sh[1][ty][tx] = sg;
+        __syncthreads();
+        if (t == 0) {
+            ll = 0.0; sg = 0.0;
+            for (int y = 0; y < kFinY; ++y)
+                for (int x = 0; x < 32; ++x) { ll += sh[0][y][x]; sg += sh[1][y][x]; }
+            float* tail = stats + total;
+            if (beta) ll += (double)tail[0] + (double)tail[1];
+            const float hi = (float)ll;
+            tail[0] = hi;
+            tail[1] = isfinite(hi) ? (float)(ll - (double)hi) : 0.f;
+            tail[2] = beta ? tail[2] + (float)sg : (float)sg;
+            tail[3] = beta ? tail[3] + (float)(*nonpd) : (float)(*nonpd);
+        }
     }
 }
 
 __global__ void finalize_ll_kernel(const double* __restrict__ part_ll, const int* __restrict__ nonpd, int nblk,
                                    double* __restrict__ out_sum, int* __restrict__ status, int beta) {
+    // one warp: lane-strided partial sums, then a fixed-order butterfly (deterministic)
+    double ll = 0.0;
+    for (int blk = threadIdx.x; blk < nblk; blk += 32) ll += part_ll[2 * blk];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ll += __shfl_xor_sync(0xffffffffu, ll, o);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        double ll = 0.0;
-        for (int blk = 0; blk < nblk; ++blk) ll += part_ll[2 * blk];
         if (out_sum) {
             out_sum[0] = beta ? out_sum[0] + ll : ll;
             out_sum[1] = beta ? out_sum[1] + (double)(*nonpd) : (double)(*nonpd);
@@ -596,8 +626,7 @@ int dgmm_estep_stats_f32(const float* X, const float* S, int noise_layout, int64
     rc = run_pair(MODE_STATS, X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, g, resp_floor, out_ll, workspace,
                   workspace_bytes, st, &plan, &ws);
     if (rc) return rc;
-    const int total = K * (1 + D + D * D) + 1;
-    finalize_stats_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
+    finalize_stats_kernel<<<ns_of(D) * ((K + 31) / 32) + 1, dim3(32, kFinY), 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
                                                                plan.GS, (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.TPB : plan.GS,
                                                                (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.NSLOT : 1, out_stats, 0);
     CUDA_TRY(cudaGetLastError());
@@ -796,8 +825,7 @@ static int stats_pass_host(dgmm_ctx* c, const float* X, const float* S, int layo
         int r = run_pair(MODE_STATS, dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr,
                          resp_floor, nullptr, c->ws, c->ws_bytes, st, &plan, &ws);
         if (r) return r;
-        const int total = K * (1 + D + D * D) + 1;
-        finalize_stats_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
+        finalize_stats_kernel<<<ns_of(D) * ((K + 31) / 32) + 1, dim3(32, kFinY), 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
                                                                    plan.GS, (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.TPB : plan.GS,
                                                                    (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.NSLOT : 1, c->d_stats, 1);
         return (int)cudaGetLastError();

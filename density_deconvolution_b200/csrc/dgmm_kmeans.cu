@@ -189,23 +189,32 @@ __global__ void __launch_bounds__(kTPB) kmeans_assign_kernel(const float* __rest
     }
 }
 
-// Sums the per-block partials in block order (double) into the packed buffer
+// Sums the per-block partials (double, fixed order: deterministic) into the packed buffer
 //   [counts (K) | sums (K*D) | dist_hi | dist_lo].
+// One warp per output: lanes take blocks b = lane, lane + 32, ..., then a fixed butterfly.
 __global__ void kmeans_finalize_kernel(const float* __restrict__ part, const double* __restrict__ part_d, int nblk,
                                        int D, int K, float* __restrict__ stats) {
     const int NC = n_chunks(D);
     const int row = NC * 4;
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int o = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);   // output handled by this warp
     const int total = K * (D + 1);
-    if (tid < total) {
-        const int j = tid / (D + 1), a = tid - j * (D + 1);  // a == D: the count column
-        double s = 0.0;
-        for (int b = 0; b < nblk; ++b) s += (double)part[((size_t)b * K + j) * row + a];
+    if (o > total) return;
+    double s = 0.0;
+    if (o < total) {
+        const int j = o / (D + 1), a = o - j * (D + 1);  // a == D: the count column
+        for (int b = lane; b < nblk; b += 32) s += (double)part[((size_t)b * K + j) * row + a];
+    } else {
+        for (int b = lane; b < nblk; b += 32) s += part_d[b];
+    }
+#pragma unroll
+    for (int x = 16; x > 0; x >>= 1) s += __shfl_xor_sync(0xffffffffu, s, x);
+    if (lane != 0) return;
+    if (o < total) {
+        const int j = o / (D + 1), a = o - j * (D + 1);
         if (a == D) stats[j] = (float)s;
         else stats[K + j * D + a] = (float)s;
-    } else if (tid == total) {
-        double s = 0.0;
-        for (int b = 0; b < nblk; ++b) s += part_d[b];
+    } else {
         const float hi = (float)s;
         stats[total] = hi;
         stats[total + 1] = isfinite(hi) ? (float)(s - (double)hi) : 0.f;
@@ -280,8 +289,8 @@ int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, const float*
     int grid = (int)std::min<long long>(km_max_grid(sms), n_tiles > 0 ? n_tiles : 1);
     fn<<<grid, kTPB, smem, st>>>(X, (long long)N, K, centroids, labels, ws.part, ws.part_d);
     CUDA_TRY(cudaGetLastError());
-    const int total = K * (D + 1) + 1;
-    kmeans_finalize_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws.part, ws.part_d, grid, D, K, out_stats);
+    const int total = K * (D + 1) + 1;                       // one warp per output, 8 warps per block
+    kmeans_finalize_kernel<<<(total + 7) / 8, 256, 0, st>>>(ws.part, ws.part_d, grid, D, K, out_stats);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

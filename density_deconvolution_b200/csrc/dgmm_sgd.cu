@@ -1,0 +1,220 @@
+// dgmm_sgd.cu -- the parameter side of one minibatch-SGD step as two small kernels, so that a
+// step of BaseSGDGMM.fit (deconv/gmm/sgd_gmm.py:167-182) is five launches of this library and no
+// autograd graph:
+//     prepare_kernel, pair_kernel<MODE_STATS>, finalize_stats_kernel      (forward + backward)
+//     [all-reduce of the packed statistics]
+//     sgd_component_kernel, sgd_weights_kernel                             (chain rule + Adam + re-parametrise)
+// What the two kernels replace, per step, in the reference:
+//   * autograd through SGDGMMModule.L / covars (sgd_gmm.py:38-47), softmax (sgd_deconv_gmm.py:17) and
+//     reg_loss (sgd_gmm.py:110-112): with the fused statistics s0, s1, S2 of sum_i ll_i
+//       d loss/d mu_j      = -s1_j / n
+//       d loss/d Sigma_j   = -S2_j / (2n)  -  (n/n_total) w diag(1 / Sigma_j[d,d]^2)      =: G_j (symmetric)
+//       d loss/d L_j       = 2 G_j L_j;   l_lower: its strict lower part, l_diag: diag * exp(l_diag)
+//       d loss/d soft_w_k  = -(s0_k - alpha_k sum_j s0_j) / n
+//   * torch.optim.Adam.step (defaults: betas (0.9, 0.999), eps 1e-8, no weight decay / amsgrad), state in
+//     caller-owned exp_avg / exp_avg_sq buffers (the estimator passes the torch optimiser's own state
+//     tensors, so `optimiser.state` stays truthful);
+//   * the next forward's parameter transform: log_alpha = log_softmax(soft_weights), Sigma_j = L_j L_j^T.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/dgmm_b200.h"
+
+namespace {
+
+#define CUDA_TRY(x)                                  \
+    do {                                             \
+        cudaError_t e__ = (x);                       \
+        if (e__ != cudaSuccess) return (int)e__;     \
+    } while (0)
+
+struct AdamCfg {
+    float lr, beta1, beta2, eps;
+    float bc1, bc2_sqrt;  // 1 - beta1^t, sqrt(1 - beta2^t)
+};
+
+// torch/optim/adam.py (_single_tensor_adam): exp_avg.lerp_(grad, 1 - beta1);
+// exp_avg_sq = beta2 exp_avg_sq + (1 - beta2) grad^2; denom = sqrt(exp_avg_sq) / sqrt(bc2) + eps;
+// param -= (lr / bc1) * exp_avg / denom
+__device__ __forceinline__ float adam_update(float p, float g, float* m, float* v, const AdamCfg& c) {
+    const float mm = *m + (g - *m) * (1.f - c.beta1);
+    const float vv = c.beta2 * *v + (1.f - c.beta2) * g * g;
+    *m = mm;
+    *v = vv;
+    const float denom = sqrtf(vv) / c.bc2_sqrt + c.eps;
+    return p - (c.lr / c.bc1) * (mm / denom);
+}
+
+__device__ __forceinline__ int low_index(int a, int b) { return a * (a - 1) / 2 + b; }  // torch.tril_indices(D, D, -1) order
+
+// One block per component, D*D threads.  update == 0: only the transform Sigma_j = L_j L_j^T.
+__global__ void sgd_component_kernel(int update, const float* __restrict__ stats, float inv_n, float reg, AdamCfg cfg,
+                                     int D, int K, float* __restrict__ means, float* __restrict__ l_diag,
+                                     float* __restrict__ l_lower, float* m_mu, float* v_mu, float* m_ld, float* v_ld,
+                                     float* m_ll, float* v_ll, float* __restrict__ Sigma) {
+    extern __shared__ float sh[];
+    float* L = sh;            // [D*D]
+    float* G = L + D * D;     // [D*D]
+    const int j = blockIdx.x, t = threadIdx.x;
+    const int a = t / D, b = t - a * D;
+    const int NL = D * (D - 1) / 2;
+    float* ld = l_diag + (size_t)j * D;
+    float* ll = l_lower + (size_t)j * NL;
+    L[t] = (a == b) ? expf(ld[a]) : (a > b ? ll[low_index(a, b)] : 0.f);
+    __syncthreads();
+    if (update) {
+        const float* s1 = stats + K + (size_t)j * D;
+        const float* S2 = stats + K + (size_t)K * D + (size_t)j * D * D;
+        float g = -0.5f * inv_n * S2[t];
+        if (a == b) {
+            float sd = 0.f;
+            for (int c = 0; c <= a; ++c) sd = fmaf(L[a * D + c], L[a * D + c], sd);   // Sigma_j[a,a]
+            g -= reg / (sd * sd);
+        }
+        G[t] = g;
+        __syncthreads();
+        float newL = L[t];
+        if (a >= b) {
+            float dl = 0.f;
+            for (int c = b; c < D; ++c) dl = fmaf(G[a * D + c], L[c * D + b], dl);    // L is lower: L[c][b] = 0 for c < b
+            dl *= 2.f;
+            if (a == b) {
+                const int i = j * D + a;
+                const float nd = adam_update(ld[a], dl * L[t], m_ld + i, v_ld + i, cfg);
+                ld[a] = nd;
+                newL = expf(nd);
+            } else {
+                const int i = j * NL + low_index(a, b);
+                newL = adam_update(ll[low_index(a, b)], dl, m_ll + i, v_ll + i, cfg);
+                ll[low_index(a, b)] = newL;
+            }
+        }
+        if (b == 0) {
+            const int i = j * D + a;
+            means[i] = adam_update(means[i], -inv_n * s1[a], m_mu + i, v_mu + i, cfg);
+        }
+        __syncthreads();
+        L[t] = newL;
+        __syncthreads();
+    }
+    const int lo = a < b ? a : b;
+    float s = 0.f;
+    for (int c = 0; c <= lo; ++c) s = fmaf(L[a * D + c], L[b * D + c], s);
+    Sigma[(size_t)j * D * D + t] = s;
+}
+
+// One block of 256 threads (K <= 256).  update == 0: only log_alpha = log_softmax(soft_weights).
+// epoch_acc (optional, 2 doubles): += (sum_i ll_i of the minibatch, non-PD pair count) from the stats tail.
+__global__ void sgd_weights_kernel(int update, const float* __restrict__ stats, float inv_n, AdamCfg cfg, int D, int K,
+                                   float* __restrict__ soft_weights, float* m_sw, float* v_sw,
+                                   float* __restrict__ log_alpha, double* epoch_acc) {
+    __shared__ float red[256];
+    __shared__ float red2[256];
+    const int t = threadIdx.x;
+    auto block_max = [&](float v) {
+        red[t] = v;
+        __syncthreads();
+        for (int o = 128; o > 0; o >>= 1) {
+            if (t < o) red[t] = fmaxf(red[t], red[t + o]);
+            __syncthreads();
+        }
+        const float r = red[0];
+        __syncthreads();
+        return r;
+    };
+    auto block_sum2 = [&](float v, float w, float& sv, float& sw) {
+        red[t] = v;
+        red2[t] = w;
+        __syncthreads();
+        for (int o = 128; o > 0; o >>= 1) {
+            if (t < o) { red[t] += red[t + o]; red2[t] += red2[t + o]; }
+            __syncthreads();
+        }
+        sv = red[0];
+        sw = red2[0];
+        __syncthreads();
+    };
+    float w = t < K ? soft_weights[t] : -INFINITY;
+    if (update) {
+        const float s0 = t < K ? stats[t] : 0.f;
+        const float mx = block_max(w);
+        const float e = t < K ? expf(w - mx) : 0.f;
+        float se, ss;
+        block_sum2(e, s0, se, ss);
+        if (t < K) {
+            const float alpha = e / se;
+            const float g = -inv_n * (s0 - alpha * ss);
+            w = adam_update(w, g, m_sw + t, v_sw + t, cfg);
+            soft_weights[t] = w;
+        }
+        if (t == 0 && epoch_acc) {
+            const float* tail = stats + (size_t)K * (1 + D + D * D);
+            epoch_acc[0] += (double)tail[0] + (double)tail[1];
+            epoch_acc[1] += (double)tail[3];
+        }
+    }
+    const float mx = block_max(w);
+    const float e = t < K ? expf(w - mx) : 0.f;
+    float se, dummy;
+    block_sum2(e, 0.f, se, dummy);
+    if (t < K) log_alpha[t] = (w - mx) - logf(se);
+}
+
+int check_shape(int D, int K) {
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (K < 1 || K > DGMM_MAX_K) return DGMM_ERR_UNSUPPORTED_K;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dgmm_sgd_params_f32(const float* soft_weights, const float* l_diag, const float* l_lower, int D, int K,
+                        float* log_alpha, float* Sigma, void* stream) {
+    int rc = check_shape(D, K);
+    if (rc) return rc;
+    if (!soft_weights || !l_diag || (D > 1 && !l_lower) || !log_alpha || !Sigma) return DGMM_ERR_BAD_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    AdamCfg cfg{};
+    sgd_component_kernel<<<K, D * D, 2 * D * D * sizeof(float), st>>>(
+        0, nullptr, 0.f, 0.f, cfg, D, K, nullptr, const_cast<float*>(l_diag), const_cast<float*>(l_lower), nullptr,
+        nullptr, nullptr, nullptr, nullptr, nullptr, Sigma);
+    CUDA_TRY(cudaGetLastError());
+    sgd_weights_kernel<<<1, 256, 0, st>>>(0, nullptr, 0.f, cfg, D, K, const_cast<float*>(soft_weights), nullptr, nullptr,
+                                          log_alpha, nullptr);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int dgmm_sgd_adam_step_f32(const float* stats, double n_batch, double n_total, float w, float lr, float beta1,
+                           float beta2, float eps, int step, int D, int K, float* soft_weights, float* means,
+                           float* l_diag, float* l_lower, float* const* exp_avg, float* const* exp_avg_sq,
+                           float* log_alpha, float* Sigma, double* epoch_acc, void* stream) {
+    int rc = check_shape(D, K);
+    if (rc) return rc;
+    if (!stats || !soft_weights || !means || !l_diag || (D > 1 && !l_lower) || !exp_avg || !exp_avg_sq || !log_alpha ||
+        !Sigma || step < 1 || !(n_batch > 0) || !(n_total > 0))
+        return DGMM_ERR_BAD_ARG;
+    for (int i = 0; i < 4; ++i)
+        if ((i != 3 || D > 1) && (!exp_avg[i] || !exp_avg_sq[i])) return DGMM_ERR_BAD_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    AdamCfg cfg;
+    cfg.lr = lr; cfg.beta1 = beta1; cfg.beta2 = beta2; cfg.eps = eps;
+    cfg.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+    cfg.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
+    const float inv_n = (float)(1.0 / n_batch);
+    const float reg = (float)(n_batch / n_total * (double)w);
+    // exp_avg / exp_avg_sq: [0] soft_weights, [1] means, [2] l_diag, [3] l_lower
+    sgd_component_kernel<<<K, D * D, 2 * D * D * sizeof(float), st>>>(1, stats, inv_n, reg, cfg, D, K, means, l_diag,
+                                                                      l_lower, exp_avg[1], exp_avg_sq[1], exp_avg[2],
+                                                                      exp_avg_sq[2], exp_avg[3], exp_avg_sq[3], Sigma);
+    CUDA_TRY(cudaGetLastError());
+    sgd_weights_kernel<<<1, 256, 0, st>>>(1, stats, inv_n, cfg, D, K, soft_weights, exp_avg[0], exp_avg_sq[0], log_alpha,
+                                          epoch_acc);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

@@ -599,7 +599,60 @@ class BaseSGDGMM:
 
     def _batches(self, data, shuffle):
         X, S = as_tensors(data)
-        return DeviceBatches((X, S), self.batch_size, self.device, shuffle=shuffle)
+        return DeviceBatches((X, S), self.batch_size, self.device, shuffle=shuffle and self.shuffle)
+
+    # ---- fused optimiser step: no autograd graph, five launches per minibatch -------------------
+    fused_step = True   # False: the autograd route (module.log_prob_sum -> loss.backward -> optimiser.step)
+    shuffle = True      # DataLoader(shuffle=True) of sgd_gmm.py:139-145; tests fix the batch order
+
+    def _fused_step_ok(self):
+        g = self.optimiser.param_groups[0]
+        return (self.fused_step and isinstance(self.module, SGDDeconvGMMModule)
+                and isinstance(self.optimiser, torch.optim.Adam) and len(self.optimiser.param_groups) == 1
+                and not g.get("weight_decay") and not g.get("amsgrad") and not g.get("maximize"))
+
+    def _adam_state(self):
+        """The parameters and the torch optimiser's OWN state tensors (created here the way
+        ``torch.optim.Adam`` creates them on its first step), so ``optimiser.state`` stays truthful."""
+        params = [self.module.soft_weights, self.module.means, self.module.l_diag, self.module.l_lower]
+        states = []
+        for prm in params:
+            st = self.optimiser.state[prm]
+            if len(st) == 0:
+                st["step"] = torch.tensor(0.0)
+                st["exp_avg"] = torch.zeros_like(prm, memory_format=torch.preserve_format)
+                st["exp_avg_sq"] = torch.zeros_like(prm, memory_format=torch.preserve_format)
+            states.append(st)
+        return params, states
+
+    def _fused_epoch(self, loader, n_total, ws):
+        """One epoch of sgd_gmm.py:167-182 on the fused kernels: per minibatch ONE statistics pass
+        (forward and backward of the loss), one all-reduce, one Adam step on the ``[K,.]`` parameters
+        (``dgmm_sgd_adam_step_f32``).  Returns the epoch's mean log-likelihood (:183)."""
+        params, states = self._adam_state()
+        group = self.optimiser.param_groups[0]
+        data = [prm.data for prm in params]
+        exp_avg = [st["exp_avg"] for st in states]
+        exp_avg_sq = [st["exp_avg_sq"] for st in states]
+        step = int(states[0]["step"].item())
+        log_alpha, Sigma = _ops.sgd_params(data[0], data[2], data[3])
+        epoch_acc = torch.zeros(2, dtype=torch.float64, device=self.device)
+        stats = None
+        for X_b, S_b in loader:
+            n = X_b.shape[0] * ws                                                # global minibatch
+            _, stats = _ops.estep_stats(X_b, S_b, log_alpha, data[1], Sigma, noise=_noise_layout(X_b, S_b),
+                                        want_ll=False, out_stats=stats)
+            _dist.allreduce_stats(stats)
+            step += 1
+            _ops.sgd_adam_step(stats, n, n_total, self.w, group["lr"], group["betas"], group["eps"], step, data,
+                               exp_avg, exp_avg_sq, log_alpha, Sigma, epoch_acc)
+        for st in states:
+            st["step"].fill_(float(step))
+        self.optimiser._opt_called = True   # what optimiser.step() records for the lr scheduler's order check
+        acc = epoch_acc.cpu()
+        if acc[1].item() > 0:
+            return math.nan
+        return acc[0].item() / n_total
 
     def fit(self, data, val_data=None, verbose=False, interval=1, init=True):
         loader = self._batches(data, shuffle=True)
@@ -613,17 +666,21 @@ class BaseSGDGMM:
             self.val_loss_curve = []
             best_val_loss, no_improvement_epochs = -math.inf, 0
         prev_loss = -math.inf
+        fused = self._fused_step_ok()
         for i in range(self.epochs):
-            epoch_ll = torch.zeros((), dtype=torch.float64, device=self.device)
-            for d in loader:
-                self.optimiser.zero_grad(set_to_none=True)
-                n = d[0].shape[0] * ws                                           # global minibatch
-                ll_sum = self.module.log_prob_sum(d)                             # sgd_gmm.py:173 (+ all-reduce)
-                loss = -ll_sum / n + self.reg_loss(n, n_total)                   # :174-179
-                epoch_ll += ll_sum.detach()                                      # :176 without the per-batch sync
-                loss.backward()                                                  # :181
-                self.optimiser.step()                                            # :182
-            train_loss = epoch_ll.item() / n_total
+            if fused:
+                train_loss = self._fused_epoch(loader, n_total, ws)
+            else:
+                epoch_ll = torch.zeros((), dtype=torch.float64, device=self.device)
+                for d in loader:
+                    self.optimiser.zero_grad(set_to_none=True)
+                    n = d[0].shape[0] * ws                                       # global minibatch
+                    ll_sum = self.module.log_prob_sum(d)                         # sgd_gmm.py:173 (+ all-reduce)
+                    loss = -ll_sum / n + self.reg_loss(n, n_total)               # :174-179
+                    epoch_ll += ll_sum.detach()                                  # :176 without the per-batch sync
+                    loss.backward()                                              # :181
+                    self.optimiser.step()                                        # :182
+                train_loss = epoch_ll.item() / n_total
             if math.isnan(train_loss):
                 raise ValueError("Sigma_j + S_i is not positive definite for some (point, component) pair")
             self.train_loss_curve.append(train_loss)

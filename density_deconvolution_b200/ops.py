@@ -339,3 +339,52 @@ def kmeans_update(mode, stats, centroids, counts_run=None):
 def kmeans_total_distance(stats):
     """``sum_i min_j |x_i - c_j|`` from the packed buffer (a float pair carrying a double)."""
     return float(stats[-2].item()) + float(stats[-1].item())
+
+
+# -----------------------------------------------------------------------------------------
+# minibatch SGD: parameter side of a step (deconv/gmm/sgd_gmm.py:167-182)
+# -----------------------------------------------------------------------------------------
+def _inplace(name, t):
+    if t is not None and not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+        raise DgmmError("%s must be a contiguous float32 CUDA tensor (updated in place)" % name)
+    return t
+
+
+def sgd_params(soft_weights, l_diag, l_lower, out_log_alpha=None, out_Sigma=None):
+    """``log_softmax(soft_weights)`` and ``Sigma_j = L_j L_j^T`` (sgd_gmm.py:38-47)."""
+    dev = soft_weights.device
+    K, D = l_diag.shape
+    for n, t in (("soft_weights", soft_weights), ("l_diag", l_diag), ("l_lower", l_lower)):
+        _inplace(n, t)
+    la = out_log_alpha if out_log_alpha is not None else torch.empty(K, dtype=torch.float32, device=dev)
+    Sg = out_Sigma if out_Sigma is not None else torch.empty(K, D, D, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_sgd_params_f32(_ptr(soft_weights), _ptr(l_diag), _ptr(l_lower if D > 1 else None), D, K,
+                                            _ptr(la), _ptr(Sg), _stream(dev))
+    check(rc, "dgmm_sgd_params_f32")
+    return la, Sg
+
+
+def sgd_adam_step(stats, n_batch, n_total, w, lr, betas, eps, step, params, exp_avg, exp_avg_sq, log_alpha, Sigma,
+                  epoch_acc=None):
+    """Chain rule + Adam + re-parametrisation from the packed statistics of one minibatch, in place.
+    ``params = (soft_weights, means, l_diag, l_lower)``; ``exp_avg`` / ``exp_avg_sq`` the matching Adam
+    moments; ``epoch_acc`` an optional float64 ``[2]`` accumulator of (sum ll, non-PD pairs)."""
+    dev = stats.device
+    sw, mu, ld, ll = params
+    K, D = mu.shape
+    for n, t in (("stats", stats), ("soft_weights", sw), ("means", mu), ("l_diag", ld), ("l_lower", ll),
+                 ("log_alpha", log_alpha), ("Sigma", Sigma)) + tuple(("exp_avg", t) for t in exp_avg) + \
+            tuple(("exp_avg_sq", t) for t in exp_avg_sq):
+        _inplace(n, t)
+    if epoch_acc is not None and not (epoch_acc.is_cuda and epoch_acc.dtype == torch.float64 and epoch_acc.numel() == 2):
+        raise DgmmError("epoch_acc must be a float64 CUDA tensor of 2 elements")
+    arr = ctypes.c_void_p * 4
+    m = arr(*[t.data_ptr() if t.numel() else None for t in exp_avg])
+    v = arr(*[t.data_ptr() if t.numel() else None for t in exp_avg_sq])
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_sgd_adam_step_f32(_ptr(stats), float(n_batch), float(n_total), float(w), float(lr),
+                                               float(betas[0]), float(betas[1]), float(eps), int(step), D, K,
+                                               _ptr(sw), _ptr(mu), _ptr(ld), _ptr(ll if D > 1 else None), m, v,
+                                               _ptr(log_alpha), _ptr(Sigma), _ptr(epoch_acc), _stream(dev))
+    check(rc, "dgmm_sgd_adam_step_f32")

@@ -198,6 +198,32 @@ DGMM_API int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, con
 DGMM_API int dgmm_kmeans_update_f32(int mode, const float* stats, int D, int K, float* centroids,
                                     float* counts_run, void* stream);
 
+/* ---- minibatch SGD: parameter side of one step (device pointers) ------------------------ */
+
+/* Parameter transform of SGDGMMModule (deconv/gmm/sgd_gmm.py:38-47, sgd_deconv_gmm.py:17):
+ *   log_alpha = log_softmax(soft_weights) [K],
+ *   Sigma_j = L_j L_j^T with L_j = strict_lower(l_lower_j) + diag(exp(l_diag_j))   [K,D,D].
+ * l_lower [K, D(D-1)/2] in the order of torch.tril_indices(D, D, -1) (may be NULL for D = 1). */
+DGMM_API int dgmm_sgd_params_f32(const float* soft_weights, const float* l_diag, const float* l_lower, int D, int K,
+                                 float* log_alpha, float* Sigma, void* stream);
+
+/* One optimiser step of BaseSGDGMM.fit (deconv/gmm/sgd_gmm.py:167-182) from the (all-reduced) packed
+ * statistics of the minibatch (dgmm_estep_stats_f32 with g = NULL, resp_floor = 0):
+ *   loss = -(1/n_batch) sum_i ll_i + (n_batch/n_total) w sum_{j,d} 1/Sigma_j[d,d]   (reg_loss, :110-112)
+ * chain rule to (soft_weights, means, l_diag, l_lower), torch.optim.Adam update (no weight decay, no
+ * amsgrad; `step` = 1-based step count for the bias corrections), then the transform of
+ * dgmm_sgd_params_f32 on the updated parameters.  All four parameter tensors, their Adam moments
+ * exp_avg[4] / exp_avg_sq[4] (HOST arrays of device pointers in the order soft_weights, means, l_diag,
+ * l_lower) are updated in place; log_alpha [K] and Sigma [K,D,D] are written for the next launch of
+ * the statistics kernel (mu is `means` itself).  epoch_acc (optional, 2 device doubles) accumulates
+ * sum_i ll_i and the non-PD pair count of the minibatches (the per-epoch train loss of :176 without
+ * a host sync per batch). */
+DGMM_API int dgmm_sgd_adam_step_f32(const float* stats, double n_batch, double n_total, float w, float lr,
+                                    float beta1, float beta2, float eps, int step, int D, int K,
+                                    float* soft_weights, float* means, float* l_diag, float* l_lower,
+                                    float* const* exp_avg, float* const* exp_avg_sq, float* log_alpha,
+                                    float* Sigma, double* epoch_acc, void* stream);
+
 /* ---- diagnostics (not part of the drop-in surface) ----------------------------------- */
 
 /* Overrides the automatic launch plan of the pair kernel; -1 = automatic for that field.

@@ -339,3 +339,45 @@ def kmeans_minibatch_update(counts, sums, centroids, counts_run):
     n_new = np.asarray(counts_run, dtype=np.float64) + counts
     C = np.asarray(centroids, dtype=np.float64)
     return C + (sums - counts[:, None] * C) / n_new[:, None], n_new
+
+
+def sgd_loss_grads_from_stats(s0, s1, S2, soft_weights, means, l_diag, l_lower, n_batch, n_total, w,
+                              dtype=np.float64):
+    """Gradient of the fit loop's loss (deconv/gmm/sgd_gmm.py:173-181)
+    ``-(1/n) sum_i ll_i + (n/n_total) w sum_{j,d} 1/Sigma_j[d,d]`` w.r.t. the four parameters, from
+    the fused statistics of ``sum_i ll_i`` (``g = 1``): autograd through sgd_gmm.py:38-47,110-112."""
+    alpha, mu, Sigma, L = sgd_to_mixture(soft_weights, means, l_diag, l_lower, dtype)
+    K, D = mu.shape
+    idx = np.arange(D)
+    d_sw = -(s0 - alpha * s0.sum()) / n_batch
+    d_mu = -s1 / n_batch
+    G = -0.5 * S2 / n_batch
+    G[:, idx, idx] -= (n_batch / n_total) * w / Sigma[:, idx, idx] ** 2
+    dL = 2.0 * np.einsum("kab,kbc->kac", G, L)
+    d_diag = dL[:, idx, idx] * np.exp(np.asarray(l_diag, dtype=dtype))
+    rows, cols = strict_lower_index(D)
+    d_low = dL[:, rows, cols] if rows.size else np.zeros((K, 0), dtype=dtype)
+    return d_sw, d_mu, d_diag, d_low
+
+
+def adam_update(p, g, m, v, lr, beta1, beta2, eps, step):
+    """torch.optim.Adam (defaults; the optimiser of deconv/gmm/sgd_gmm.py:92-95), one tensor."""
+    m = m + (g - m) * (1.0 - beta1)
+    v = beta2 * v + (1.0 - beta2) * g * g
+    bc1 = 1.0 - beta1 ** step
+    bc2 = 1.0 - beta2 ** step
+    denom = np.sqrt(v) / np.sqrt(bc2) + eps
+    return p - (lr / bc1) * (m / denom), m, v
+
+
+def sgd_adam_step(stats3, params, moments, n_batch, n_total, w, lr, beta1, beta2, eps, step):
+    """One optimiser step of BaseSGDGMM.fit (sgd_gmm.py:167-182) from ``stats3 = (s0, s1, S2)``.
+    ``params`` / ``moments = (exp_avg list, exp_avg_sq list)`` in the order soft_weights, means,
+    l_diag, l_lower.  Returns ``(new_params, new_exp_avg, new_exp_avg_sq)``."""
+    grads = sgd_loss_grads_from_stats(*stats3, *params, n_batch, n_total, w)
+    new_p, new_m, new_v = [], [], []
+    for p, g, m, v in zip(params, grads, moments[0], moments[1]):
+        a, b, c = adam_update(np.asarray(p, np.float64), g, np.asarray(m, np.float64), np.asarray(v, np.float64),
+                              lr, beta1, beta2, eps, step)
+        new_p.append(a); new_m.append(b); new_v.append(c)
+    return new_p, new_m, new_v

@@ -140,3 +140,33 @@ def kmeans_update(mode, stats, centroids, counts_run=None):
 
 def kmeans_total_distance(stats):
     return float(stats[-2].item()) + float(stats[-1].item())
+
+
+# ---- minibatch SGD parameter side (ops.sgd_*) ----------------------------------------------------
+def sgd_params(soft_weights, l_diag, l_lower, out_log_alpha=None, out_Sigma=None):
+    K, D = l_diag.shape
+    alpha, _, Sigma, _ = orc.sgd_to_mixture(_np(soft_weights), np.zeros((K, D)), _np(l_diag), _np(l_lower))
+    la = torch.tensor(np.log(alpha), dtype=torch.float32, device=soft_weights.device)
+    Sg = torch.tensor(Sigma, dtype=torch.float32, device=soft_weights.device)
+    if out_log_alpha is not None:
+        out_log_alpha.copy_(la); la = out_log_alpha
+    if out_Sigma is not None:
+        out_Sigma.copy_(Sg); Sg = out_Sigma
+    return la, Sg
+
+
+def sgd_adam_step(stats, n_batch, n_total, w, lr, betas, eps, step, params, exp_avg, exp_avg_sq, log_alpha, Sigma,
+                  epoch_acc=None):
+    K, D = params[1].shape
+    s = _np(stats)
+    s0, s1, S2 = s[:K], s[K:K + K * D].reshape(K, D), s[K + K * D:K + K * D + K * D * D].reshape(K, D, D)
+    new_p, new_m, new_v = orc.sgd_adam_step((s0, s1, S2), [_np(p) for p in params],
+                                            ([_np(m) for m in exp_avg], [_np(v) for v in exp_avg_sq]),
+                                            n_batch, n_total, w, lr, betas[0], betas[1], eps, step)
+    with torch.no_grad():
+        for dst, src in zip(list(params) + list(exp_avg) + list(exp_avg_sq), new_p + new_m + new_v):
+            dst.copy_(torch.tensor(src, dtype=torch.float32).reshape(dst.shape))
+    sgd_params(params[0], params[2], params[3], out_log_alpha=log_alpha, out_Sigma=Sigma)
+    if epoch_acc is not None:
+        epoch_acc[0] += float(s[-4]) + float(s[-3])
+        epoch_acc[1] += float(s[-1])

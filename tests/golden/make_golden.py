@@ -297,7 +297,52 @@ def kmeans_case(name):
     print(name, sorted(out))
 
 
+def sgd_fit_case(name, N, D, K, dtype, epochs=7, batch=16):
+    """The inner loop of BaseSGDGMM.fit (deconv/gmm/sgd_gmm.py:163-186) on the reference's own module,
+    reg_loss, Adam optimiser and MultiStepLR scheduler, with injected parameters and the batches taken
+    in order (the reference's DataLoader shuffles; everything else is its code path)."""
+    rng = np.random.default_rng(2024)
+    X, S, _, mu, _ = synth(rng, N, D, K)
+    torch.set_default_dtype(dtype)
+    m = SGDDeconvGMM(K, D, w=1e-3, batch_size=batch, lr=2e-2, lr_step=2)
+    sw = rng.standard_normal(K)
+    l_diag = 0.3 * rng.standard_normal((K, D))
+    l_lower = 0.5 * rng.standard_normal((K, D * (D - 1) // 2))
+    m.module.soft_weights.data = torch.tensor(sw, dtype=dtype)
+    m.module.means.data = torch.tensor(mu, dtype=dtype)
+    m.module.l_diag.data = torch.tensor(l_diag, dtype=dtype)
+    m.module.l_lower.data = torch.tensor(l_lower, dtype=dtype)
+    tX, tS = torch.tensor(X, dtype=dtype), torch.tensor(S, dtype=dtype)
+    out = dict(X=X, S=S, soft_weights=sw, means=mu, l_diag=l_diag, l_lower=l_lower)
+    curve = []
+    for ep in range(epochs):
+        train_loss = 0.0
+        for lo in range(0, N, batch):
+            d = [tX[lo:lo + batch], tS[lo:lo + batch]]
+            m.optimiser.zero_grad()
+            log_prob = m.module(d)
+            loss = -1 * torch.mean(log_prob)
+            train_loss += torch.sum(log_prob).item()
+            loss += m.reg_loss(d[0].shape[0], N)
+            loss.backward()
+            m.optimiser.step()
+        curve.append(train_loss / N)
+        m.scheduler.step()
+        if ep + 1 in (1, 3, epochs):
+            for pn in ("soft_weights", "means", "l_diag", "l_lower"):
+                out["%s_after_%d" % (pn, ep + 1)] = getattr(m.module, pn).detach().numpy().copy()
+    out["train_loss_curve"] = np.asarray(curve)
+    out["lr_final"] = m.optimiser.param_groups[0]["lr"]
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, curve)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "sgd_fit":
+        sgd_fit_case("ref_sgd_fit_d5_k3_f32.npz", N=64, D=5, K=3, dtype=torch.float32)
+        sgd_fit_case("ref_sgd_fit_d3_k4_f64.npz", N=48, D=3, K=4, dtype=torch.float64)
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "kmeans":
         kmeans_case("ref_kmeans.npz")
         return
@@ -314,6 +359,8 @@ def main():
     robustness_case("ref_robust_f32.npz")
     boston_case("ref_boston_k10_f64.npz")
     kmeans_case("ref_kmeans.npz")
+    sgd_fit_case("ref_sgd_fit_d5_k3_f32.npz", N=64, D=5, K=3, dtype=torch.float32)
+    sgd_fit_case("ref_sgd_fit_d3_k4_f64.npz", N=48, D=3, K=4, dtype=torch.float64)
 
 
 if __name__ == "__main__":

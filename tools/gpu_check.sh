@@ -10,7 +10,7 @@ import json
 for l in open("gpurun_out/chk_$wl.json"):
     if l.startswith("{"):
         d=json.loads(l); r=d["roofline"]
-        print("$wl", "EM ms %.2f frac %.3f | loglik ms %.2f frac %.3f" % (r["launch_ms"], r["frac"], r["loglik_kernel"]["launch_ms"], r["loglik_kernel"]["frac"]))
+        print("$wl", "EM ms %.2f frac %.3f | loglik ms %.2f frac %.3f" % (r["launch_ms"], r["frac"], r["loglik_kernel"]["launch_ms"], r["loglik_kernel"]["frac"]), "| sgd", d.get("sgd"))
 PY
   tail -n 2 gpurun_out/chk_$wl.err
 done
