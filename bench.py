@@ -51,6 +51,15 @@ def F_em(D):
     return D ** 3 + 6.5 * D ** 2 + 10.5 * D + 10
 
 
+def ncu_traffic(workload, kernel):
+    """DRAM bytes per launch of ``kernel`` measured by ncu on this workload (None if not captured)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f).get(workload, {}).get(kernel)
+    except (OSError, ValueError):
+        return None
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -331,7 +340,9 @@ def run_b200(args, wl):
                     "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)",
         flops_per_pair=F_em(D), pairs_per_launch=N * K, launch_ms=pair_avg_s * 1e3,
         share_of_step=pair_avg_s * args.steps / t_em if world == 1 else None,
-        traffic=None,
+        traffic=ncu_traffic(args.workload, "pair_kernel<MODE_STATS>") if not args.points else None,
+        traffic_note="DRAM bytes per launch from the committed ncu --set full capture (profiles/ncu_traffic.json); "
+                     "algorithmic bytes per launch = %d" % (N * bytes_per_point),
         hbm=dict(achieved=N * bytes_per_point / pair_avg_s / 1e9, peak=hbm_peak, unit="GB/s",
                  frac=N * bytes_per_point / pair_avg_s / 1e9 / hbm_peak,
                  peak_source="MEASURED_PEAKS.json" if peaks else "fallback of B200_PROFILING.md"),

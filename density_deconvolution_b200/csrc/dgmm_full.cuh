@@ -29,6 +29,22 @@ struct FullParams {
     int K, noise;
 };
 
+// posterior sampling (sample_kernel): one thread per (point, draw)
+struct SampleParams {
+    const float* X;
+    const float* S;
+    const float* mu;         // [K,D]
+    const float* Sigma;      // [K,D,D]
+    const float* log_r;      // [N,K]  log responsibilities (full_kernel)
+    const float* u;          // [N,M]  uniforms in [0,1)
+    const float* z;          // [N,M,D] standard normals
+    float* out;              // [N,M,D]
+    int* out_comp;           // [N,M] picked component, or null
+    int* nonpd;              // counts draws whose B_ij was not positive definite
+    long long N;
+    int K, M, noise;
+};
+
 }  // namespace dgmm
 
 #define DGMM_LOOP _Pragma("unroll")

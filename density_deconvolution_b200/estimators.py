@@ -787,16 +787,22 @@ class SGDDeconvGMM(BaseSGDGMM):
             out[lo:lo + step] = self._sample(min(step, num_samples - lo)).to(device)
         return out
 
-    def _sample_posterior(self, x, num_samples, context=None):
-        """sgd_deconv_gmm.py:107-119 -> ``[N, num_samples, D]``: picks a component per draw from
-        ``r_i`` and samples ``N(b_ij, B_ij)`` only for the picked components."""
-        log_r, b, B = self.posterior_params(x)
-        n = log_r.shape[0]
-        idx = torch.multinomial(torch.exp(log_r), num_samples, replacement=True)        # [N,M]
-        rows = torch.arange(n, device=self.device)[:, None]
-        L = torch.linalg.cholesky(B[rows, idx])                                          # [N,M,D,D]
-        eps = torch.randn(n, num_samples, self.d, device=self.device)
-        return b[rows, idx] + torch.einsum("nmab,nmb->nma", L, eps)
+    def _sample_posterior(self, x, num_samples, context=None, generator=None):
+        """sgd_deconv_gmm.py:107-119 -> ``[N, num_samples, D]``: a component per draw from ``r_i`` and a
+        draw of ``N(b_ij, B_ij)`` for the picked component only, in one kernel
+        (``dgmm_posterior_sample_f32``); no ``[N,K,D,D]`` tensor is formed."""
+        with torch.no_grad():
+            X = _resident(x[0], self.device)
+            S = _resident(x[1], self.device)
+            log_alpha, mu, Sigma = self.module._mixture_tensors()
+            n = X.shape[0]
+            u = torch.rand(n, num_samples, device=self.device, generator=generator)
+            z = torch.randn(n, num_samples, self.d, device=self.device, generator=generator)
+            out, _, _, status = _ops.posterior_sample(X, S, log_alpha.contiguous(), mu.contiguous(),
+                                                      Sigma.contiguous(), u, z, noise=_noise_layout(X, S))
+        if int(status.item()) != 0:
+            raise ValueError("a posterior covariance B_ij (or some Sigma_j + S_i) is not positive definite")
+        return out
 
     def sample_posterior(self, x, num_samples, device=torch.device("cpu")):
         """sgd_deconv_gmm.py:121-130."""

@@ -388,3 +388,37 @@ def sgd_adam_step(stats, n_batch, n_total, w, lr, betas, eps, step, params, exp_
                                                _ptr(sw), _ptr(mu), _ptr(ld), _ptr(ll if D > 1 else None), m, v,
                                                _ptr(log_alpha), _ptr(Sigma), _ptr(epoch_acc), _stream(dev))
     check(rc, "dgmm_sgd_adam_step_f32")
+
+
+# -----------------------------------------------------------------------------------------
+# posterior sampling (deconv/gmm/sgd_deconv_gmm.py:107-119) without [N,K,D,D] tensors
+# -----------------------------------------------------------------------------------------
+def posterior_sample(X, S, log_alpha, mu, Sigma, u, z, noise="full", want_comp=False):
+    """``u [N,M]`` uniforms pick the component (inverse CDF of ``r_i``), ``z [N,M,D]`` standard normals
+    give ``b_ij + chol(B_ij) z``.  Returns ``(samples [N,M,D], comp int32 [N,M] or None, log_r [N,K],
+    status)``."""
+    X = _f32c(X, "X")
+    dev = X.device
+    N, D = X.shape
+    log_alpha, mu, Sigma, K, D2 = _params(log_alpha, mu, Sigma, dev)
+    if D2 != D:
+        raise ValueError("X has D=%d, parameters have D=%d" % (D, D2))
+    S, code = _noise(S, noise, N, D, dev)
+    u = _f32c(u, "u", dev)
+    z = _f32c(z, "z", dev)
+    if u.dim() != 2 or u.shape[0] != N or tuple(z.shape) != (N, u.shape[1], D):
+        raise ValueError("u must be [N,M] and z [N,M,D]; got %s and %s" % (tuple(u.shape), tuple(z.shape)))
+    M = u.shape[1]
+    out = torch.empty(N, M, D, dtype=torch.float32, device=dev)
+    comp = torch.empty(N, M, dtype=torch.int32, device=dev) if want_comp else None
+    log_r = torch.empty(N, K, dtype=torch.float32, device=dev)
+    ll = torch.empty(N, dtype=torch.float32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws = workspace(D, K, dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_posterior_sample_f32(_ptr(X), _ptr(S), code, N, D, K, _ptr(log_alpha), _ptr(mu),
+                                                  _ptr(Sigma), M, _ptr(u), _ptr(z), _ptr(out), _ptr(comp),
+                                                  _ptr(log_r), _ptr(ll), _ptr(status), _ptr(ws), ws.numel(),
+                                                  _stream(dev))
+    check(rc, "dgmm_posterior_sample_f32")
+    return out, comp, log_r, status

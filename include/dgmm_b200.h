@@ -198,6 +198,24 @@ DGMM_API int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, con
 DGMM_API int dgmm_kmeans_update_f32(int mode, const float* stats, int D, int K, float* centroids,
                                     float* counts_run, void* stream);
 
+/* ---- posterior sampling (device pointers) ------------------------------------------------ */
+
+/* M draws per point from the posterior mixture p(v | w_i, S_i) = sum_j r_ij N(b_ij, B_ij) without
+ * materialising b [N,K,D] or B [N,K,D,D].  Replaces SGDDeconvGMM._sample_posterior
+ * (deconv/gmm/sgd_deconv_gmm.py:107-119; the exact-baseline sampler of the flow experiments,
+ * deconv/flow/svi_gmm.py:21-32).  The caller supplies the randomness, so the call is a deterministic
+ * map: u [N,M] uniforms in [0,1) pick the component by inverse CDF of r_i (first j with
+ * cumsum_j r_ij > u), z [N,M,D] standard normals give the draw b_ij + chol(B_ij) z, which is how
+ * torch.distributions.MultivariateNormal(loc, covariance_matrix).sample maps its normals.
+ *   out_samples [N,M,D]; out_comp (optional) [N,M] int32 picked components; scratch_log_r [N,K]
+ *   (receives log r_ij); out_ll [N] (receives ll_i); status (optional, 1 device int): non-PD
+ *   (point,component) pairs plus draws whose B_ij had a non-positive pivot (those samples are NaN). */
+DGMM_API int dgmm_posterior_sample_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                                       const float* log_alpha, const float* mu, const float* Sigma, int M,
+                                       const float* u, const float* z, float* out_samples, int32_t* out_comp,
+                                       float* scratch_log_r, float* out_ll, int* status, void* workspace,
+                                       size_t workspace_bytes, void* stream);
+
 /* ---- minibatch SGD: parameter side of one step (device pointers) ------------------------ */
 
 /* Parameter transform of SGDGMMModule (deconv/gmm/sgd_gmm.py:38-47, sgd_deconv_gmm.py:17):

@@ -381,3 +381,23 @@ def sgd_adam_step(stats3, params, moments, n_batch, n_total, w, lr, beta1, beta2
                               lr, beta1, beta2, eps, step)
         new_p.append(a); new_m.append(b); new_v.append(c)
     return new_p, new_m, new_v
+
+
+def posterior_sample(X, S, alpha, mu, Sigma, u, z, dtype=np.float64):
+    """SGDDeconvGMM._sample_posterior (deconv/gmm/sgd_deconv_gmm.py:107-119) as a deterministic map
+    of the caller's randomness: ``u [N,M]`` -> component by inverse CDF of ``r_i`` (what
+    ``Categorical(logits=p_weights).sample`` draws), ``z [N,M,D]`` -> ``b_ij + cholesky(B_ij) z`` (what
+    ``MultivariateNormal(loc, covariance_matrix).sample`` does with its standard normals:
+    torch/distributions/multivariate_normal.py rsample = loc + scale_tril @ eps).
+    Returns ``(samples [N,M,D], comp [N,M], cdf [N,K])``."""
+    _, (log_r, b, B), _ = e_step(X, S, alpha, mu, Sigma, dtype)
+    cdf = np.cumsum(np.exp(log_r), axis=1)
+    N, M = np.asarray(u).shape
+    K = cdf.shape[1]
+    comp = np.minimum((np.asarray(u, dtype)[:, :, None] >= cdf[:, None, :]).sum(axis=2), K - 1)
+    out = np.zeros((N, M, b.shape[2]), dtype=dtype)
+    for i in range(N):
+        for m in range(M):
+            j = comp[i, m]
+            out[i, m] = b[i, j] + np.linalg.cholesky(B[i, j]) @ np.asarray(z, dtype)[i, m]
+    return out, comp, cdf

@@ -170,3 +170,15 @@ def sgd_adam_step(stats, n_batch, n_total, w, lr, betas, eps, step, params, exp_
     if epoch_acc is not None:
         epoch_acc[0] += float(s[-4]) + float(s[-3])
         epoch_acc[1] += float(s[-1])
+
+
+# ---- posterior sampling (ops.posterior_sample) ---------------------------------------------------
+def posterior_sample(X, S, log_alpha, mu, Sigma, u, z, noise="full", want_comp=False):
+    Sn = _full_noise(X, S, noise)
+    out, comp, cdf = orc.posterior_sample(_np(X), Sn, np.exp(_np(log_alpha)), _np(mu), _np(Sigma), _np(u), _np(z))
+    r = np.diff(np.concatenate([np.zeros((cdf.shape[0], 1)), cdf], axis=1), axis=1)
+    dev = X.device
+    return (torch.tensor(out, dtype=torch.float32, device=dev),
+            torch.tensor(comp, dtype=torch.int32, device=dev) if want_comp else None,
+            torch.tensor(np.log(np.maximum(r, 1e-300)), dtype=torch.float32, device=dev),
+            torch.zeros(1, dtype=torch.int32, device=dev))

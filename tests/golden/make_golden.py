@@ -338,7 +338,38 @@ def sgd_fit_case(name, N, D, K, dtype, epochs=7, batch=16):
     print(name, curve)
 
 
+def posterior_sample_case(name, N=4, D=3, K=4, M=60000):
+    """Monte-Carlo moments of the reference's SGDDeconvGMM._sample_posterior (sgd_deconv_gmm.py:107-119):
+    its torch RNG streams cannot be reproduced elsewhere, its distribution can."""
+    rng = np.random.default_rng(99)
+    X, S, _, mu, _ = synth(rng, N, D, K, spread=1.5)
+    torch.set_default_dtype(torch.float64)
+    m = SGDDeconvGMM(K, D, w=1e-3, batch_size=16)
+    sw = 0.5 * rng.standard_normal(K)
+    l_diag = 0.3 * rng.standard_normal((K, D))
+    l_lower = 0.5 * rng.standard_normal((K, D * (D - 1) // 2))
+    m.module.soft_weights.data = torch.tensor(sw)
+    m.module.means.data = torch.tensor(mu)
+    m.module.l_diag.data = torch.tensor(l_diag)
+    m.module.l_lower.data = torch.tensor(l_lower)
+    m.device = torch.device("cpu")
+    torch.manual_seed(7)
+    with torch.no_grad():
+        smp = m._sample_posterior((torch.tensor(X), torch.tensor(S)), M).numpy()   # [N,M,D]
+        pw, pm, pc = m.posterior_params((torch.tensor(X), torch.tensor(S)))
+    mean = smp.mean(axis=1)
+    cov = np.stack([np.cov(smp[i].T) for i in range(N)])
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), X=X, S=S, soft_weights=sw, means=mu, l_diag=l_diag, l_lower=l_lower,
+                        M=M, sample_mean=mean, sample_cov=cov, post_log_w=pw.numpy(), post_means=pm.numpy(),
+                        post_covars=pc.numpy())
+    print(name, mean)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "posterior_sample":
+        posterior_sample_case("ref_posterior_sample.npz")
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "sgd_fit":
         sgd_fit_case("ref_sgd_fit_d5_k3_f32.npz", N=64, D=5, K=3, dtype=torch.float32)
         sgd_fit_case("ref_sgd_fit_d3_k4_f64.npz", N=48, D=3, K=4, dtype=torch.float64)
@@ -361,6 +392,7 @@ def main():
     kmeans_case("ref_kmeans.npz")
     sgd_fit_case("ref_sgd_fit_d5_k3_f32.npz", N=64, D=5, K=3, dtype=torch.float32)
     sgd_fit_case("ref_sgd_fit_d3_k4_f64.npz", N=48, D=3, K=4, dtype=torch.float64)
+    posterior_sample_case("ref_posterior_sample.npz")
 
 
 if __name__ == "__main__":
