@@ -358,9 +358,13 @@ bool fit_geometry(const DeviceInfo& dev, const PairVariant& v, int mode, int D, 
     while (GS * nslot > v.max_threads && nslot > 1) --nslot;
     if (GS * nslot > v.max_threads) return false;
     while (GS * nslot < 32) ++nslot;                   // whole warps only (full-mask shuffles)
-    const int pt0 = (D <= 10) ? 16 : (D <= 16 ? 8 : 4);
+    // D <= 10: 16 points per slot and tile (the per-tile costs -- barrier, ring refill, the
+    // log-likelihood pass's logsumexp sweep -- are amortised over 16 trips of the point loop), as long
+    // as three blocks still fit in an SM's shared memory; measured sweep: profiles/r01_pt_sweep.txt
+    int pt0 = (D <= 10) ? std::min(16 * nslot, 64) : (D <= 16 ? 8 : 4);
     int nst = (D <= 16) ? 3 : 2;
     if (t.nst > 0) nst = std::min(t.nst, kMaxStages);
+    const size_t smem_3blocks = (size_t)74 * 1024;
     for (;;) {
         int PT = t.pt > 0 ? t.pt : pt0;
         int lcm = nslot;                               // PT: a multiple of NSLOT and of 4
@@ -369,6 +373,10 @@ bool fit_geometry(const DeviceInfo& dev, const PairVariant& v, int mode, int D, 
         const size_t smem = pair_smem_bytes(D, noise, has_g, v.sigp, v.accp, GS, GS * nslot, PT, nst, mode);
         const bool tmem_ok = v.accp != ST_TMEM || mode != MODE_STATS ||
                              tmem_alloc_cols(ns_of(D), GS * nslot / 32) <= 512;
+        if (D <= 10 && t.pt <= 0 && smem > smem_3blocks && v.min_blocks >= 3) {
+            if (nst > 2 && t.nst <= 0) { nst = 2; continue; }
+            if (pt0 > 16 && pt0 / 2 >= lcm) { pt0 /= 2; nst = (t.nst > 0) ? nst : 3; continue; }
+        }
         if (smem <= (size_t)dev.smem_optin && tmem_ok) {
             p->NSLOT = nslot; p->TPB = GS * nslot; p->PT = PT; p->NST = nst; p->smem = smem;
             return true;
