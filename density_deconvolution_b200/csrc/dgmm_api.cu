@@ -331,9 +331,10 @@ struct Plan {
 };
 
 size_t pair_smem_bytes(int D, int noise, bool has_g, int sigp, int accp, int GS, int TPB, int PT, int NST,
-                       int mode) {
+                       int mode, int nz) {
     const StageLayout SL = stage_layout(D, noise, PT, has_g);
     size_t b = kSmemHeader + (size_t)NST * SL.bytes;
+    if (repack_noise(D, nz)) b += (size_t)PT * D * ((D + 3) & ~3) * 4;   // re-packed lower triangles of the tile
     if (sigp == ST_SMEM) b += (size_t)pad_col(nd_of(D)) * GS * 4;
     if (mode == MODE_STATS && accp == ST_SMEM) b += (size_t)pad_col(ns_of(D)) * TPB * 4;
     if (mode == MODE_LOGLIK) b += (size_t)2 * PT * (GS + 16) * 4;  // deferred logsumexp rows
@@ -370,7 +371,7 @@ bool fit_geometry(const DeviceInfo& dev, const PairVariant& v, int mode, int D, 
         int lcm = nslot;                               // PT: a multiple of NSLOT and of 4
         while (lcm % 4) lcm += nslot;
         PT = ((PT + lcm - 1) / lcm) * lcm;
-        const size_t smem = pair_smem_bytes(D, noise, has_g, v.sigp, v.accp, GS, GS * nslot, PT, nst, mode);
+        const size_t smem = pair_smem_bytes(D, noise, has_g, v.sigp, v.accp, GS, GS * nslot, PT, nst, mode, v.nz);
         const bool tmem_ok = v.accp != ST_TMEM || mode != MODE_STATS ||
                              tmem_alloc_cols(ns_of(D), GS * nslot / 32) <= 512;
         if (D <= 10 && t.pt <= 0 && smem > smem_3blocks && v.min_blocks >= 3) {

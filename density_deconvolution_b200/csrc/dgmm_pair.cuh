@@ -179,6 +179,12 @@ __host__ __device__ inline int lse_lanes(int TPB, int PT) {
     return r;
 }
 
+// Full per-point noise with odd D: the pair kernel re-packs the tile's lower triangles into 16-byte
+// aligned rows (compiled placements with a fixed noise class only).
+__host__ __device__ constexpr bool repack_noise(int D, int nz) {
+    return nz == NZ_FULL && (D & 1) && D > 1 && D <= DGMM_UNROLL_D;
+}
+
 // Bytes of one ring stage and the offsets of its three sub-tiles (all multiples of 16).
 __host__ __device__ inline int noise_floats_per_point(int D, int noise) {
     return noise == NOISE_FULL ? D * D : (noise == NOISE_DIAG ? D : 0);
