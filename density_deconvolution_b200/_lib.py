@@ -23,7 +23,8 @@ _ERRORS = {
 # every symbol include/dgmm_b200.h declares (tests check the list against the header)
 SYMBOLS = (
     "dgmm_abi_version", "dgmm_supported_dims", "dgmm_workspace_bytes", "dgmm_loglik_f32",
-    "dgmm_estep_stats_f32", "dgmm_estep_full_f32", "dgmm_mstep_update_f32", "dgmm_fp32_probe",
+    "dgmm_estep_stats_f32", "dgmm_estep_full_f32", "dgmm_mstep_update_f32", "dgmm_online_mstep_f32",
+    "dgmm_fp32_probe",
     "dgmm_ctx_create", "dgmm_ctx_destroy", "dgmm_em_iteration_host", "dgmm_estep_stats_host", "dgmm_score_host",
     "dgmm_kmeans_workspace_bytes", "dgmm_kmeans_assign_f32", "dgmm_kmeans_update_f32",
     "dgmm_posterior_sample_f32", "dgmm_sgd_params_f32", "dgmm_sgd_adam_step_f32",
@@ -77,6 +78,8 @@ def lib():
     L.dgmm_estep_full_f32.argtypes = [vp, vp, i32, i64, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     L.dgmm_mstep_update_f32.restype = i32
     L.dgmm_mstep_update_f32.argtypes = [vp, f64, f32, i32, i32, vp, vp, vp, vp, vp]
+    L.dgmm_online_mstep_f32.restype = i32
+    L.dgmm_online_mstep_f32.argtypes = [vp, f32, f32, f32, f64, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
     L.dgmm_fp32_probe.restype = i32
     L.dgmm_fp32_probe.argtypes = [vp, i32, ctypes.POINTER(f64), vp]
     L.dgmm_ctx_create.restype = i32

@@ -292,6 +292,80 @@ __global__ void mstep_kernel(const float* __restrict__ stats, double n_total, do
     }
 }
 
+// Online-EM M-step of one minibatch from the packed statistics; one block per component, D*D threads,
+// double precision inside.  deconv/gmm/online_deconv_gmm.py:146-188 via SURVEY.md Appendix C:
+//   batch: sr = s0 + floor, scm = s0 mu + Sigma s1, bm = scm / sr,
+//          bc = [s0 (Sigma + c c^T) + Sigma S2 Sigma + c v^T + v c^T] / sr   (c = mu - bm, v = Sigma s1)
+//   EMA:   SR' = (1-g) SR + g sr, SCM' = (1-g) SCM + g scm, mu' = SCM' / SR'
+//   Sigma' = (1-g) adj(Sigma - wI, SR/SR', mu, mu') + g adj(bc, sr/SR', bm, mu') + wI,
+//            adj(C, s, b, c) = s (C + b b^T) - c c^T   (_adjust, :134-144);   alpha' = SR' / global_batch.
+// A minibatch with a non-PD pair leaves everything untouched and sets the sticky crash flag (:79-80).
+__global__ void online_mstep_kernel(const float* __restrict__ stats, double floor_, double g, double w,
+                                    double global_batch, int D, int K, float* __restrict__ mu,
+                                    float* __restrict__ Sigma, float* __restrict__ SR, float* __restrict__ SCM,
+                                    float* __restrict__ alpha, float* __restrict__ log_alpha,
+                                    int* __restrict__ crash) {
+    extern __shared__ double sh[];
+    double* Sg = sh;            // [D*D]
+    double* S2 = Sg + D * D;    // [D*D]
+    double* W = S2 + D * D;     // [D*D]  Sigma S2
+    double* v = W + D * D;      // [D]    Sigma s1
+    const int j = blockIdx.x, t = threadIdx.x;
+    const int a = t / D, b = t - a * D;
+    const float* tail = stats + (size_t)K * (1 + D + D * D);
+    if ((crash && *crash) || tail[3] > 0.f) {
+        if (crash && j == 0 && t == 0) *crash = 1;
+        return;
+    }
+    const double s0 = (double)stats[j];
+    const float* s1 = stats + K + (size_t)j * D;
+    const float* s2 = stats + K + (size_t)K * D + (size_t)j * D * D;
+    float* Sj = Sigma + (size_t)j * D * D;
+    float* muj = mu + (size_t)j * D;
+    Sg[t] = (double)Sj[a >= b ? a * D + b : b * D + a];
+    S2[t] = (double)s2[t];
+    __syncthreads();
+    double acc = 0.0;
+    for (int c = 0; c < D; ++c) acc += Sg[a * D + c] * S2[c * D + b];
+    W[t] = acc;
+    if (b == 0) {
+        double vv = 0.0;
+        for (int c = 0; c < D; ++c) vv += Sg[a * D + c] * (double)s1[c];
+        v[a] = vv;
+    }
+    __syncthreads();
+    double P = 0.0;
+    for (int c = 0; c < D; ++c) P += W[a * D + c] * Sg[c * D + b];
+    const double sr = s0 + floor_;
+    const double mua = (double)muj[a], mub = (double)muj[b];
+    const double scm_a = s0 * mua + v[a], scm_b = s0 * mub + v[b];
+    const double bm_a = scm_a / sr, bm_b = scm_b / sr;
+    const double ca = mua - bm_a, cb = mub - bm_b;
+    const double bc = (s0 * (Sg[t] + ca * cb) + P + ca * v[b] + v[a] * cb) / sr;
+    const double sr_old = (double)SR[j];
+    const double sr_new = (1.0 - g) * sr_old + g * sr;
+    const double scmn_a = (1.0 - g) * (double)SCM[(size_t)j * D + a] + g * scm_a;
+    const double scmn_b = (1.0 - g) * (double)SCM[(size_t)j * D + b] + g * scm_b;
+    const double mn_a = scmn_a / sr_new, mn_b = scmn_b / sr_new;
+    const double so = sr_old / sr_new, sb = sr / sr_new;
+    const double wd = (a == b) ? w : 0.0;
+    const double old_part = so * ((Sg[t] - wd) + mua * mub) - mn_a * mn_b;
+    const double new_part = sb * (bc + bm_a * bm_b) - mn_a * mn_b;
+    const double cov = (1.0 - g) * old_part + g * new_part + wd;
+    __syncthreads();   // every read of mu / SCM / SR of this component is done
+    Sj[t] = (float)cov;
+    if (b == 0) {
+        muj[a] = (float)mn_a;
+        SCM[(size_t)j * D + a] = (float)scmn_a;
+    }
+    if (t == 0) {
+        SR[j] = (float)sr_new;
+        const double al = sr_new / global_batch;
+        alpha[j] = (float)al;
+        log_alpha[j] = (float)log(al);
+    }
+}
+
 __global__ void log_kernel(const float* __restrict__ in, float* __restrict__ out, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = logf(in[i]);
@@ -715,6 +789,21 @@ int dgmm_mstep_update_f32(const float* stats, double n_total, float w, int D, in
     if (!stats || !mu || !Sigma || !alpha || !log_alpha) return DGMM_ERR_BAD_ARG;
     const size_t sh = (size_t)(3 * D * D + D) * sizeof(double);
     mstep_kernel<<<K, D * D, sh, (cudaStream_t)stream>>>(stats, n_total, (double)w, D, K, mu, Sigma, alpha, log_alpha);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int dgmm_online_mstep_f32(const float* stats, float resp_floor, float step_size, float w, double global_batch,
+                          int D, int K, float* mu, float* Sigma, float* sum_resps, float* sum_cond_means,
+                          float* alpha, float* log_alpha, int* crash_flag, void* stream) {
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (K < 1) return DGMM_ERR_UNSUPPORTED_K;
+    if (!stats || !mu || !Sigma || !sum_resps || !sum_cond_means || !alpha || !log_alpha || !(global_batch > 0))
+        return DGMM_ERR_BAD_ARG;
+    const size_t sh = (size_t)(3 * D * D + D) * sizeof(double);
+    online_mstep_kernel<<<K, D * D, sh, (cudaStream_t)stream>>>(stats, (double)resp_floor, (double)step_size,
+                                                                 (double)w, global_batch, D, K, mu, Sigma, sum_resps,
+                                                                 sum_cond_means, alpha, log_alpha, crash_flag);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -273,23 +273,19 @@ class OnlineDeconvGMM(DeconvGMM):
         self.sum_resps = self.weights * self._global_batch()
         self.sum_cond_means = self.means * self.sum_resps
 
-    def _m_step_stats(self, stats, step_size):
-        """online_deconv_gmm.py:146-188 written on the fused statistics."""
-        s0, s1, S2, _ = _ops.unpack_stats(stats, self.d, self.k)
-        mu, Sigma = self.means, self.covars
-        sum_resps = (s0 + self.resp_floor)[:, None]                              # :152-154
-        sum_cond_means = _alg.sum_resp_means(s0, s1, mu, Sigma)                  # :156
-        batch_means = sum_cond_means / sum_resps                                 # :157
-        batch_covars = _alg.centred_scatter(s0, s1, S2, mu, Sigma, batch_means) / sum_resps[:, :, None]  # :159-166
-        m_old, sum_old = mu, self.sum_resps
-        self.sum_resps = (1 - step_size) * sum_old + step_size * sum_resps       # :171
-        self.sum_cond_means = (1 - step_size) * self.sum_cond_means + step_size * sum_cond_means
-        self.means = self.sum_cond_means / self.sum_resps                        # :174
-        self.covars = ((1 - step_size) * _alg.moment_shift(Sigma - self.w, sum_old / self.sum_resps, m_old, self.means)
-                       + step_size * _alg.moment_shift(batch_covars, sum_resps / self.sum_resps, batch_means,
-                                                       self.means)
-                       + self.w)                                                 # :176-186
-        self.weights = self.sum_resps / self._global_batch()                     # :188
+    def _m_step_stats(self, stats, step_size, log_alpha=None, crash_flag=None):
+        """online_deconv_gmm.py:146-188 on the fused statistics: ONE kernel
+        (``dgmm_online_mstep_f32``) moves ``sum_resps, sum_cond_means, means, covars, weights`` in place."""
+        for name in ("weights", "means", "covars", "sum_resps", "sum_cond_means"):
+            t = getattr(self, name)
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                setattr(self, name, t.to(torch.float32).contiguous())
+        if log_alpha is None:
+            log_alpha = torch.empty(self.k, dtype=torch.float32, device=self.device)
+        _ops.online_mstep(stats, self.resp_floor, step_size, self.w_scalar, self._global_batch(), self.means,
+                          self.covars, self.sum_resps.view(-1), self.sum_cond_means, self.weights.view(-1),
+                          log_alpha, crash_flag)
+        return log_alpha
 
     def _m_step(self, expectations, n, step_size):
         """Reference signature (online_deconv_gmm.py:146) on materialised expectations."""
@@ -326,19 +322,21 @@ class OnlineDeconvGMM(DeconvGMM):
             self.val_ll_curve = []
         stats = torch.empty(_ops.stats_len(self.d, self.k), dtype=torch.float32, device=self.device)
         prev_ll, max_val_ll, no_improvements = -math.inf, -math.inf, 0
+        # per minibatch: statistics kernel -> (all-reduce) -> M-step kernel; no host sync inside an epoch
+        # (a non-PD minibatch freezes the state through the sticky device flag, read once per epoch)
+        self.weights, self.means, self.covars = (t.to(torch.float32).contiguous()
+                                                 for t in (self.weights, self.means, self.covars))
+        log_alpha = torch.log(self.weights.view(-1))
+        crash_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         for i in range(self.epochs):
-            crashed = False
             seen = 0
             for Xb, Sb in loader:
-                mix = self._mixture()
-                _ops.estep_stats(Xb, Sb, mix.log_alpha, mix.mu, mix.Sigma, resp_floor=self.resp_floor, noise=layout,
+                _ops.estep_stats(Xb, Sb, log_alpha, self.means, self.covars, resp_floor=self.resp_floor, noise=layout,
                                  want_ll=False, out_stats=stats)
                 _dist.allreduce_stats(stats)
-                if stats[-1].item() > 0:                                         # online_deconv_gmm.py:79-80
-                    crashed = True
-                    break
-                self._m_step_stats(stats, self.step_size)
+                self._m_step_stats(stats, self.step_size, log_alpha, crash_flag)  # online_deconv_gmm.py:79-80 inside
                 seen += 1
+            crashed = bool(crash_flag.item())
             if crashed or seen == 0:                                             # :84-88
                 print("Log prob 0, crashed.")
                 break

@@ -422,3 +422,23 @@ def posterior_sample(X, S, log_alpha, mu, Sigma, u, z, noise="full", want_comp=F
                                                   _stream(dev))
     check(rc, "dgmm_posterior_sample_f32")
     return out, comp, log_r, status
+
+
+def online_mstep(stats, resp_floor, step_size, w, global_batch, mu, Sigma, sum_resps, sum_cond_means, alpha, log_alpha,
+                 crash_flag=None):
+    """In-place Online-EM M-step of one minibatch (online_deconv_gmm.py:134-188) from packed statistics.
+    ``sum_resps [K]`` (or ``[K,1]``), ``sum_cond_means [K,D]``, ``alpha [K]`` / ``log_alpha [K]`` are updated
+    with ``mu`` and ``Sigma``; ``crash_flag`` is an optional int32 ``[1]`` device tensor (sticky)."""
+    dev = stats.device
+    K, D = mu.shape
+    for n, t in (("stats", stats), ("means", mu), ("covars", Sigma), ("sum_resps", sum_resps),
+                 ("sum_cond_means", sum_cond_means), ("alpha", alpha), ("log_alpha", log_alpha)):
+        _inplace(n, t)
+    if crash_flag is not None and not (crash_flag.is_cuda and crash_flag.dtype == torch.int32):
+        raise DgmmError("crash_flag must be an int32 CUDA tensor")
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_online_mstep_f32(_ptr(stats), float(resp_floor), float(step_size), float(w),
+                                              float(global_batch), D, K, _ptr(mu), _ptr(Sigma), _ptr(sum_resps),
+                                              _ptr(sum_cond_means), _ptr(alpha), _ptr(log_alpha), _ptr(crash_flag),
+                                              _stream(dev))
+    check(rc, "dgmm_online_mstep_f32")

@@ -126,6 +126,20 @@ DGMM_API int dgmm_estep_full_f32(const float* X, const float* S, int noise_layou
 DGMM_API int dgmm_mstep_update_f32(const float* stats, double n_total, float w, int D, int K,
                           float* mu, float* Sigma, float* alpha, float* log_alpha, void* stream);
 
+/* Online-EM M-step of one minibatch from the (all-reduced) packed statistics, in place
+ * (OnlineDeconvGMM._m_step + _adjust, deconv/gmm/online_deconv_gmm.py:134-188; the statistics come from
+ * dgmm_estep_stats_f32 with resp_floor = 10 eps, :150,154):
+ *   running sums sum_resps [K] and sum_cond_means [K,D] are moved by `step_size` towards the batch's,
+ *   mu = sum_cond_means / sum_resps, Sigma by the moment-shift rule of _adjust, alpha = sum_resps /
+ *   global_batch; log_alpha is written for the next launch of the statistics kernel.
+ * crash_flag (optional, 1 device int, caller-zeroed): a minibatch whose statistics carry a non-PD pair
+ * leaves all state untouched and sets the flag, and so does every later call while it is set (the
+ * reference breaks out of the epoch there, :79-88) -- no host synchronisation per minibatch. */
+DGMM_API int dgmm_online_mstep_f32(const float* stats, float resp_floor, float step_size, float w,
+                                   double global_batch, int D, int K, float* mu, float* Sigma, float* sum_resps,
+                                   float* sum_cond_means, float* alpha, float* log_alpha, int* crash_flag,
+                                   void* stream);
+
 /* Register-only FFMA chain used to measure the sustained FP32 roofline denominator on the
  * box (MEASURED_PEAKS.json has no FP32 entry).  Launches one kernel on `stream`;
  * returns the number of FLOPs it executes through *flops.  sink = 1 device float. */

@@ -182,3 +182,36 @@ def posterior_sample(X, S, log_alpha, mu, Sigma, u, z, noise="full", want_comp=F
             torch.tensor(comp, dtype=torch.int32, device=dev) if want_comp else None,
             torch.tensor(np.log(np.maximum(r, 1e-300)), dtype=torch.float32, device=dev),
             torch.zeros(1, dtype=torch.int32, device=dev))
+
+
+# ---- Online-EM M-step (ops.online_mstep): the [K,.] algebra of online_deconv_gmm.py:146-188 in float64 ----
+def online_mstep(stats, resp_floor, step_size, w, global_batch, mu, Sigma, sum_resps, sum_cond_means, alpha, log_alpha,
+                 crash_flag=None):
+    from density_deconvolution_b200 import stats_algebra as alg
+    K, D = mu.shape
+    if (crash_flag is not None and int(crash_flag.item())) or float(stats[-1]) > 0:
+        if crash_flag is not None:
+            crash_flag.fill_(1)
+        return
+    s = stats.double()
+    s0, s1, S2 = s[:K], s[K:K + K * D].view(K, D), s[K + K * D:K + K * D + K * D * D].view(K, D, D)
+    m_old, Sg = mu.double(), Sigma.double()
+    Sg = torch.tril(Sg) + torch.tril(Sg, -1).transpose(1, 2)
+    wI = w * torch.eye(D, dtype=torch.float64)
+    sr = (s0 + resp_floor)[:, None]
+    scm = alg.sum_resp_means(s0, s1, m_old, Sg)
+    bm = scm / sr
+    bc = alg.centred_scatter(s0, s1, S2, m_old, Sg, bm) / sr[:, :, None]
+    sum_old = sum_resps.double().view(K, 1)
+    sr_new = (1 - step_size) * sum_old + step_size * sr
+    scm_new = (1 - step_size) * sum_cond_means.double() + step_size * scm
+    m_new = scm_new / sr_new
+    cov = ((1 - step_size) * alg.moment_shift(Sg - wI, sum_old / sr_new, m_old, m_new)
+           + step_size * alg.moment_shift(bc, sr / sr_new, bm, m_new) + wI)
+    sum_resps.copy_(sr_new.view(sum_resps.shape).float())
+    sum_cond_means.copy_(scm_new.float())
+    mu.copy_(m_new.float())
+    Sigma.copy_(cov.float())
+    al = (sr_new / global_batch).view(-1)
+    alpha.copy_(al.view(alpha.shape).float())
+    log_alpha.copy_(al.log().float())
