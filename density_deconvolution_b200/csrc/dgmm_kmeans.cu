@@ -38,7 +38,7 @@ namespace {
 constexpr int kTPB = 128;          // threads per block
 constexpr int kPPT = 2;            // points per thread in phase 1
 constexpr int kTile = kTPB * kPPT; // points per tile
-constexpr int kBlocksPerSM = 4;
+constexpr int kBlocksPerSM = 8;   // upper bound of resident blocks per SM (the grid follows the occupancy query)
 
 __host__ __device__ constexpr int row_stride(int D) { return 4 * ((((D + 1) + 3) / 4) | 1); }  // floats, 4 * odd
 __host__ __device__ constexpr int cen_stride(int D) { return (D + 3) & ~3; }
@@ -286,7 +286,10 @@ int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, const float*
     const assign_fn fn = kAssign[D];
     CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long n_tiles = (N + kTile - 1) / kTile;
-    int grid = (int)std::min<long long>(km_max_grid(sms), n_tiles > 0 ? n_tiles : 1);
+    int occ = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kTPB, smem));
+    occ = std::max(1, std::min(occ, kBlocksPerSM));
+    int grid = (int)std::min<long long>((long long)sms * occ, n_tiles > 0 ? n_tiles : 1);
     fn<<<grid, kTPB, smem, st>>>(X, (long long)N, K, centroids, labels, ws.part, ws.part_d);
     CUDA_TRY(cudaGetLastError());
     const int total = K * (D + 1) + 1;                       // one warp per output, 8 warps per block
