@@ -18,7 +18,8 @@
 #define DGMM_DECL(D)                                                          \
     dgmm::PairVariant dgmm_pair_lookup_d##D(int mode, int which, int gcls, int nz); \
     const void* dgmm_full_lookup_d##D();                                      \
-    const void* dgmm_sample_lookup_d##D();
+    const void* dgmm_sample_lookup_d##D();                                    \
+    const void* dgmm_post_logprob_lookup_d##D();
 DGMM_DECL(1) DGMM_DECL(2) DGMM_DECL(3) DGMM_DECL(4) DGMM_DECL(5) DGMM_DECL(6) DGMM_DECL(7) DGMM_DECL(8)
 DGMM_DECL(9) DGMM_DECL(10) DGMM_DECL(11) DGMM_DECL(12) DGMM_DECL(13) DGMM_DECL(14) DGMM_DECL(15) DGMM_DECL(16)
 DGMM_DECL(17) DGMM_DECL(18) DGMM_DECL(19) DGMM_DECL(20) DGMM_DECL(21) DGMM_DECL(22) DGMM_DECL(23) DGMM_DECL(24)
@@ -32,14 +33,15 @@ using namespace dgmm;
 typedef PairVariant (*pair_lookup_t)(int, int, int, int);
 typedef const void* (*full_lookup_t)();
 
-#define DGMM_ROW(D) {dgmm_pair_lookup_d##D, dgmm_full_lookup_d##D, dgmm_sample_lookup_d##D}
+#define DGMM_ROW(D) {dgmm_pair_lookup_d##D, dgmm_full_lookup_d##D, dgmm_sample_lookup_d##D, dgmm_post_logprob_lookup_d##D}
 struct DimRow {
     pair_lookup_t pair;
     full_lookup_t full;
     full_lookup_t sample;
+    full_lookup_t post_logprob;
 };
 const DimRow kDims[DGMM_MAX_D + 1] = {
-    {nullptr, nullptr, nullptr},
+    {nullptr, nullptr, nullptr, nullptr},
     DGMM_ROW(1),  DGMM_ROW(2),  DGMM_ROW(3),  DGMM_ROW(4),  DGMM_ROW(5),  DGMM_ROW(6),  DGMM_ROW(7),  DGMM_ROW(8),
     DGMM_ROW(9),  DGMM_ROW(10), DGMM_ROW(11), DGMM_ROW(12), DGMM_ROW(13), DGMM_ROW(14), DGMM_ROW(15), DGMM_ROW(16),
     DGMM_ROW(17), DGMM_ROW(18), DGMM_ROW(19), DGMM_ROW(20), DGMM_ROW(21), DGMM_ROW(22), DGMM_ROW(23), DGMM_ROW(24),
@@ -774,6 +776,37 @@ int dgmm_posterior_sample_f32(const float* X, const float* S, int noise_layout, 
         if (blocks > 0x7fffffffLL) return DGMM_ERR_BAD_ARG;
         void* args[] = {&sp};
         CUDA_TRY(cudaLaunchKernel(kDims[D].sample(), dim3((unsigned)blocks), dim3(128), args, 0, st));
+    }
+    if (status) {
+        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, 0, nullptr, status, 0);
+        CUDA_TRY(cudaGetLastError());
+    }
+    return 0;
+}
+
+int dgmm_posterior_logprob_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                               const float* log_alpha, const float* mu, const float* Sigma, int M, const float* V,
+                               float* out_logprob, float* scratch_log_r, float* out_ll, int* status, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+    if (M < 1 || !V || !out_logprob || !scratch_log_r) return DGMM_ERR_BAD_ARG;
+    int rc = dgmm_estep_full_f32(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, scratch_log_r, nullptr, nullptr,
+                                 out_ll, nullptr, workspace, workspace_bytes, stream);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    DeviceInfo dev;
+    rc = device_info(&dev);
+    if (rc) return rc;
+    const Workspace ws = carve(workspace, D, K, dev.sms);
+    if (N > 0) {
+        SampleParams sp;
+        sp.X = X; sp.S = S; sp.mu = mu; sp.Sigma = Sigma; sp.log_r = scratch_log_r; sp.u = nullptr; sp.z = V;
+        sp.out = out_logprob; sp.out_comp = nullptr; sp.nonpd = ws.nonpd; sp.N = N; sp.K = K; sp.M = M;
+        sp.noise = noise_layout;
+        const long long q = (long long)N * M;
+        const long long blocks = (q + 127) / 128;
+        if (blocks > 0x7fffffffLL) return DGMM_ERR_BAD_ARG;
+        void* args[] = {&sp};
+        CUDA_TRY(cudaLaunchKernel(kDims[D].post_logprob(), dim3((unsigned)blocks), dim3(128), args, 0, st));
     }
     if (status) {
         finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, 0, nullptr, status, 0);

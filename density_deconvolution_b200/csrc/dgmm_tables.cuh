@@ -108,16 +108,26 @@ inline const void* sample_lookup() {
         return reinterpret_cast<const void*>(&rolled::sample_kernel<D>);
 }
 
+template <int D>
+inline const void* post_logprob_lookup() {
+    if constexpr (D <= DGMM_UNROLL_D)
+        return reinterpret_cast<const void*>(&unrolled::post_logprob_kernel<D>);
+    else
+        return reinterpret_cast<const void*>(&rolled::post_logprob_kernel<D>);
+}
+
 }  // namespace dgmm
 
 #define DGMM_DECLARE_DIM(D)                                                  \
     extern "C++" dgmm::PairVariant dgmm_pair_lookup_d##D(int mode, int which, int gcls, int nz); \
     extern "C++" const void* dgmm_full_lookup_d##D();                        \
-    extern "C++" const void* dgmm_sample_lookup_d##D();
+    extern "C++" const void* dgmm_sample_lookup_d##D();                      \
+    extern "C++" const void* dgmm_post_logprob_lookup_d##D();
 
 #define DGMM_DEFINE_DIM(D)                                                                      \
     dgmm::PairVariant dgmm_pair_lookup_d##D(int mode, int which, int gcls, int nz) {             \
         return dgmm::pair_lookup<D>(mode, which, gcls, nz);                                      \
     }                                                                                           \
     const void* dgmm_full_lookup_d##D() { return dgmm::full_lookup<D>(); }                      \
-    const void* dgmm_sample_lookup_d##D() { return dgmm::sample_lookup<D>(); }
+    const void* dgmm_sample_lookup_d##D() { return dgmm::sample_lookup<D>(); }                  \
+    const void* dgmm_post_logprob_lookup_d##D() { return dgmm::post_logprob_lookup<D>(); }

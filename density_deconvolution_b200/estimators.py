@@ -765,14 +765,25 @@ class SGDDeconvGMM(BaseSGDGMM):
         return log_r, b, B
 
     def posterior_log_prob(self, x, context):
-        """sgd_deconv_gmm.py:96-105: log density of ``x`` (``[N,D]`` or ``[N,M,D]``) under each
-        point's posterior mixture."""
-        p_weights, p_means, p_covars = self.posterior_params(context)
-        mvn = torch.distributions.MultivariateNormal(loc=p_means, covariance_matrix=p_covars)
-        if x.dim() == 2:
-            return torch.logsumexp(mvn.log_prob(x[:, None, None, :].to(self.device)) + p_weights, dim=2)
-        lp = mvn.log_prob(x.to(self.device).transpose(0, 1)[:, :, None, :])
-        return torch.logsumexp(lp + p_weights, dim=2).transpose(0, 1)
+        """sgd_deconv_gmm.py:96-105: log density of ``x`` (``[N,D]`` -> ``[N]``... one query per context
+        point gives ``[N,N]`` in the reference's broadcasting; ``[N,M,D]`` -> ``[N,M]``) under each context
+        point's posterior mixture, in one kernel (``dgmm_posterior_logprob_f32``): no ``[N,K,D,D]`` tensor."""
+        with torch.no_grad():
+            X = _resident(context[0], self.device)
+            S = _resident(context[1], self.device)
+            n = X.shape[0]
+            xq = _resident(x, self.device)
+            if xq.dim() == 2:
+                # reference: log_prob(x[:, None, None, :]) against [N,K] posteriors -> [len(x), N]
+                V = xq[None, :, :].expand(n, xq.shape[0], self.d).contiguous()
+            else:
+                V = xq.contiguous()
+            log_alpha, mu, Sigma = self.module._mixture_tensors()
+            out, status = _ops.posterior_logprob(X, S, log_alpha.contiguous(), mu.contiguous(), Sigma.contiguous(), V,
+                                                 noise=_noise_layout(X, S))
+        if int(status.item()) != 0:
+            raise ValueError("a posterior covariance B_ij (or some Sigma_j + S_i) is not positive definite")
+        return out.transpose(0, 1) if xq.dim() == 2 else out
 
     def _sample_prior(self, num_samples, context=None):
         return self._sample(num_samples)

@@ -442,3 +442,30 @@ def online_mstep(stats, resp_floor, step_size, w, global_batch, mu, Sigma, sum_r
                                               _ptr(sum_cond_means), _ptr(alpha), _ptr(log_alpha), _ptr(crash_flag),
                                               _stream(dev))
     check(rc, "dgmm_online_mstep_f32")
+
+
+def posterior_logprob(X, S, log_alpha, mu, Sigma, V, noise="full"):
+    """``out[i,m] = logsumexp_j(log r_ij + log N(V[i,m] | b_ij, B_ij))`` (sgd_deconv_gmm.py:96-105) for
+    ``V [N,M,D]``.  Returns ``(logprob [N,M], status)``."""
+    X = _f32c(X, "X")
+    dev = X.device
+    N, D = X.shape
+    log_alpha, mu, Sigma, K, D2 = _params(log_alpha, mu, Sigma, dev)
+    if D2 != D:
+        raise ValueError("X has D=%d, parameters have D=%d" % (D, D2))
+    S, code = _noise(S, noise, N, D, dev)
+    V = _f32c(V, "V", dev)
+    if V.dim() != 3 or V.shape[0] != N or V.shape[2] != D:
+        raise ValueError("V must be [N,M,D]; got %s" % (tuple(V.shape),))
+    M = V.shape[1]
+    out = torch.empty(N, M, dtype=torch.float32, device=dev)
+    log_r = torch.empty(N, K, dtype=torch.float32, device=dev)
+    ll = torch.empty(N, dtype=torch.float32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws = workspace(D, K, dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_posterior_logprob_f32(_ptr(X), _ptr(S), code, N, D, K, _ptr(log_alpha), _ptr(mu),
+                                                   _ptr(Sigma), M, _ptr(V), _ptr(out), _ptr(log_r), _ptr(ll),
+                                                   _ptr(status), _ptr(ws), ws.numel(), _stream(dev))
+    check(rc, "dgmm_posterior_logprob_f32")
+    return out, status

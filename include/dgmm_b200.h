@@ -230,6 +230,16 @@ DGMM_API int dgmm_posterior_sample_f32(const float* X, const float* S, int noise
                                        float* scratch_log_r, float* out_ll, int* status, void* workspace,
                                        size_t workspace_bytes, void* stream);
 
+/* Log-density of query points V [N,M,D] under each point's posterior mixture,
+ *   out_logprob[i,m] = logsumexp_j ( log r_ij + log N(V[i,m] | b_ij, B_ij) ),
+ * without materialising b or B.  Replaces SGDDeconvGMM.posterior_log_prob
+ * (deconv/gmm/sgd_deconv_gmm.py:96-105).  scratch_log_r [N,K], out_ll [N], status as for
+ * dgmm_posterior_sample_f32. */
+DGMM_API int dgmm_posterior_logprob_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
+                                        const float* log_alpha, const float* mu, const float* Sigma, int M,
+                                        const float* V, float* out_logprob, float* scratch_log_r, float* out_ll,
+                                        int* status, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- minibatch SGD: parameter side of one step (device pointers) ------------------------ */
 
 /* Parameter transform of SGDGMMModule (deconv/gmm/sgd_gmm.py:38-47, sgd_deconv_gmm.py:17):

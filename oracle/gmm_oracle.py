@@ -401,3 +401,18 @@ def posterior_sample(X, S, alpha, mu, Sigma, u, z, dtype=np.float64):
             j = comp[i, m]
             out[i, m] = b[i, j] + np.linalg.cholesky(B[i, j]) @ np.asarray(z, dtype)[i, m]
     return out, comp, cdf
+
+
+def posterior_log_prob(X, S, alpha, mu, Sigma, V, dtype=np.float64):
+    """SGDDeconvGMM.posterior_log_prob (deconv/gmm/sgd_deconv_gmm.py:96-105) for ``V [N,M,D]``:
+    ``logsumexp_j(log r_ij + log N(V[i,m] | b_ij, B_ij))`` -> ``[N,M]``."""
+    _, (log_r, b, B), _ = e_step(X, S, alpha, mu, Sigma, dtype)
+    V = np.asarray(V, dtype=dtype)
+    N, M, D = V.shape
+    L = np.linalg.cholesky(B)                                   # [N,K,D,D]
+    diff = V[:, :, None, :] - b[:, None, :, :]                   # [N,M,K,D]
+    y = np.linalg.solve(L[:, None], diff[..., None])[..., 0]
+    maha = (y ** 2).sum(axis=-1)
+    hld = np.log(np.diagonal(L, axis1=-2, axis2=-1)).sum(axis=-1)   # [N,K]
+    lp = log_r[:, None, :] - 0.5 * D * np.log(2 * np.pi) - hld[:, None, :] - 0.5 * maha
+    return _logsumexp(lp, axis=2)

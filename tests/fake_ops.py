@@ -215,3 +215,9 @@ def online_mstep(stats, resp_floor, step_size, w, global_batch, mu, Sigma, sum_r
     al = (sr_new / global_batch).view(-1)
     alpha.copy_(al.view(alpha.shape).float())
     log_alpha.copy_(al.log().float())
+
+
+def posterior_logprob(X, S, log_alpha, mu, Sigma, V, noise="full"):
+    Sn = _full_noise(X, S, noise)
+    out = orc.posterior_log_prob(_np(X), Sn, np.exp(_np(log_alpha)), _np(mu), _np(Sigma), _np(V))
+    return torch.tensor(out, dtype=torch.float32, device=X.device), torch.zeros(1, dtype=torch.int32, device=X.device)

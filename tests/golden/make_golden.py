@@ -359,11 +359,17 @@ def posterior_sample_case(name, N=4, D=3, K=4, M=60000):
         pw, pm, pc = m.posterior_params((torch.tensor(X), torch.tensor(S)))
     mean = smp.mean(axis=1)
     cov = np.stack([np.cov(smp[i].T) for i in range(N)])
+    # posterior_log_prob (sgd_deconv_gmm.py:96-105) for [N,M,D] and [Q,D] queries
+    Vq = X[:, None, :] + rng.standard_normal((N, 3, D))
+    x2 = X[:3] + 0.5 * rng.standard_normal((3, D))
+    with torch.no_grad():
+        lp3 = m.posterior_log_prob(torch.tensor(Vq), (torch.tensor(X), torch.tensor(S))).numpy()
+        lp2 = m.posterior_log_prob(torch.tensor(x2), (torch.tensor(X), torch.tensor(S))).numpy()
     torch.set_default_dtype(torch.float32)
     np.savez_compressed(os.path.join(HERE, name), X=X, S=S, soft_weights=sw, means=mu, l_diag=l_diag, l_lower=l_lower,
                         M=M, sample_mean=mean, sample_cov=cov, post_log_w=pw.numpy(), post_means=pm.numpy(),
-                        post_covars=pc.numpy())
-    print(name, mean)
+                        post_covars=pc.numpy(), query3=Vq, query2=x2, logprob3=lp3, logprob2=lp2)
+    print(name, mean, lp3.shape, lp2.shape)
 
 
 def main():

@@ -134,3 +134,44 @@ def test_sample_kernel_full_size_moments():
     # component frequencies follow the responsibilities
     freq = torch.bincount(comp.flatten().long(), minlength=K).double() / (N * M)
     assert torch.all((freq - s0.double() / N).abs() < 6 * (freq / (N * M)).sqrt() + 1e-4)
+
+
+# ---- posterior_log_prob (sgd_deconv_gmm.py:96-105) -------------------------------------------------
+def test_oracle_posterior_log_prob_matches_reference():
+    z = golden("ref_posterior_sample.npz")
+    alpha, mu, Sigma, _ = orc.sgd_to_mixture(z["soft_weights"], z["means"], z["l_diag"], z["l_lower"])
+    got = orc.posterior_log_prob(z["X"], z["S"], alpha, mu, Sigma, z["query3"])
+    np.testing.assert_allclose(got, z["logprob3"], rtol=1e-9, atol=1e-9)
+
+
+def test_estimator_posterior_log_prob_matches_reference(device):
+    from density_deconvolution_b200 import SGDDeconvGMM
+    z = golden("ref_posterior_sample.npz")
+    K, D = z["means"].shape
+    m = SGDDeconvGMM(K, D, w=1e-3, batch_size=16, device=device)
+    with torch.no_grad():
+        for p in ("soft_weights", "means", "l_diag", "l_lower"):
+            getattr(m.module, p).copy_(t32(z[p], device))
+    ctx = (t32(z["X"], device), t32(z["S"], device))
+    lp3 = m.posterior_log_prob(t32(z["query3"], device), ctx).cpu().numpy()
+    assert lp3.shape == z["logprob3"].shape
+    np.testing.assert_allclose(lp3, z["logprob3"], rtol=2e-4, atol=2e-4)
+    lp2 = m.posterior_log_prob(t32(z["query2"], device), ctx).cpu().numpy()
+    assert lp2.shape == z["logprob2"].shape                      # [Q, N]: every query against every context
+    np.testing.assert_allclose(lp2, z["logprob2"], rtol=2e-4, atol=2e-3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,K", [(1, 3), (3, 4), (10, 64), (16, 8), (20, 5)])
+def test_logprob_kernel_against_oracle(D, K):
+    from density_deconvolution_b200 import ops
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(D * 10 + K)
+    N, M = 23, 4
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    V = X[:, None, :] + rng.standard_normal((N, M, D))
+    out, status = ops.posterior_logprob(t32(X, dev), t32(S, dev), t32(np.log(alpha), dev), t32(mu, dev), t32(Sigma, dev),
+                                        t32(V, dev))
+    assert status.item() == 0
+    want = orc.posterior_log_prob(X, S, alpha, mu, Sigma, V.astype(np.float32))
+    np.testing.assert_allclose(out.cpu().numpy(), want, rtol=5e-4, atol=5e-3)
