@@ -27,7 +27,7 @@ SYMBOLS = (
     "dgmm_fp32_probe",
     "dgmm_ctx_create", "dgmm_ctx_destroy", "dgmm_em_iteration_host", "dgmm_estep_stats_host", "dgmm_score_host",
     "dgmm_kmeans_workspace_bytes", "dgmm_kmeans_assign_f32", "dgmm_kmeans_update_f32",
-    "dgmm_posterior_sample_f32", "dgmm_posterior_logprob_f32", "dgmm_sgd_params_f32", "dgmm_sgd_adam_step_f32",
+    "dgmm_gather_points_f32", "dgmm_posterior_sample_f32", "dgmm_posterior_logprob_f32", "dgmm_sgd_params_f32", "dgmm_sgd_adam_step_f32",
     "dgmm_debug_set_tuning", "dgmm_debug_get_plan", "dgmm_debug_pair_timing", "dgmm_debug_pair_times",
 )
 
@@ -99,6 +99,8 @@ def lib():
     L.dgmm_kmeans_assign_f32.argtypes = [vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
     L.dgmm_kmeans_update_f32.restype = i32
     L.dgmm_kmeans_update_f32.argtypes = [i32, vp, i32, i32, vp, vp, vp]
+    L.dgmm_gather_points_f32.restype = i32
+    L.dgmm_gather_points_f32.argtypes = [vp, vp, i32, vp, i64, i32, vp, vp, vp]
     L.dgmm_posterior_sample_f32.restype = i32
     L.dgmm_posterior_sample_f32.argtypes = [vp, vp, i32, i64, i32, i32, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp,
                                             vp, sz, vp]

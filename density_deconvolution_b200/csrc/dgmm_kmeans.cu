@@ -241,6 +241,35 @@ __global__ void kmeans_update_kernel(int mode, const float* __restrict__ stats, 
     }
 }
 
+// Minibatch gather for the device-resident batch iterator: rows idx[b] of X [N,D] and
+// of the noise table [N,n_s] (n_s = D*D, D or 0) -> contiguous outX [B,D], outS [B,n_s], one launch.
+// Replaces the per-sample __getitem__ + collate of the reference's DataLoader
+// (deconv/gmm/data.py:7-17, sgd_gmm.py:139-145).  One warp per point; 128-bit copies when the rows allow.
+__global__ void gather_points_kernel(const float* __restrict__ X, const float* __restrict__ S,
+                                     const long long* __restrict__ idx, long long B, int D, int n_s,
+                                     float* __restrict__ outX, float* __restrict__ outS) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const bool vec = (n_s & 3) == 0 && ((((uintptr_t)S) | ((uintptr_t)outS)) & 15) == 0;
+    for (long long b = warp; b < B; b += nwarps) {
+        const long long i = idx[b];
+        const float* xs = X + (size_t)i * D;
+        float* xd = outX + (size_t)b * D;
+        for (int a = lane; a < D; a += 32) xd[a] = __ldg(xs + a);
+        if (n_s == 0) continue;
+        const float* ss = S + (size_t)i * n_s;
+        float* sd = outS + (size_t)b * n_s;
+        if (vec) {
+            const float4* s4 = reinterpret_cast<const float4*>(ss);
+            float4* d4 = reinterpret_cast<float4*>(sd);
+            for (int a = lane; a < n_s / 4; a += 32) d4[a] = __ldg(s4 + a);
+        } else {
+            for (int a = lane; a < n_s; a += 32) sd[a] = __ldg(ss + a);
+        }
+    }
+}
+
 typedef void (*assign_fn)(const float*, long long, int, const float*, int*, float*, double*);
 template <int D>
 assign_fn assign_entry() { return &kmeans_assign_kernel<D>; }
@@ -294,6 +323,25 @@ int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, const float*
     CUDA_TRY(cudaGetLastError());
     const int total = K * (D + 1) + 1;                       // one warp per output, 8 warps per block
     kmeans_finalize_kernel<<<(total + 7) / 8, 256, 0, st>>>(ws.part, ws.part_d, grid, D, K, out_stats);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int dgmm_gather_points_f32(const float* X, const float* S, int noise_layout, const int64_t* idx, int64_t B, int D,
+                           float* outX, float* outS, void* stream) {
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (noise_layout != DGMM_NOISE_FULL && noise_layout != DGMM_NOISE_DIAG && noise_layout != DGMM_NOISE_NONE)
+        return DGMM_ERR_LAYOUT;
+    const int n_s = noise_layout == DGMM_NOISE_FULL ? D * D : (noise_layout == DGMM_NOISE_DIAG ? D : 0);
+    if (B < 0 || (B > 0 && (!X || !idx || !outX || (n_s && (!S || !outS))))) return DGMM_ERR_BAD_ARG;
+    if (B == 0) return 0;
+    int sms = 0, optin = 0;
+    int rc = km_device(&sms, &optin);
+    if (rc) return rc;
+    const long long want = (B + 7) / 8;                       // 8 warps per block, one point per warp and trip
+    const int grid = (int)std::min<long long>(want, (long long)sms * 16);
+    gather_points_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, S, (const long long*)idx, (long long)B, D, n_s,
+                                                                 outX, outS);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

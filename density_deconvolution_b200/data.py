@@ -41,9 +41,9 @@ class DeviceBatches:
     """Iterates ``(X_b, S_b)`` minibatches that already live on ``device``.
 
     The whole table is uploaded once (float32); every epoch draws a permutation on the device
-    and gathers batches there.  Semantics of ``DataLoader(batch_size, shuffle, drop_last)``."""
+    and gathers batches there (one ``dgmm_gather_points_f32`` launch per batch when ``ops`` is given).  Semantics of ``DataLoader(batch_size, shuffle, drop_last)``."""
 
-    def __init__(self, data, batch_size, device, shuffle=False, drop_last=False, generator=None):
+    def __init__(self, data, batch_size, device, shuffle=False, drop_last=False, generator=None, ops=None):
         X, S = as_tensors(data)
         self.X = X.to(device=device, dtype=torch.float32).contiguous()
         self.S = S.to(device=device, dtype=torch.float32).contiguous()
@@ -53,6 +53,9 @@ class DeviceBatches:
         self.drop_last = drop_last
         self.device = device
         self.generator = generator
+        # ops.gather_points: X and S rows of a shuffled batch in ONE launch (dgmm_gather_points_f32)
+        per_point = self.S.dim() in (2, 3) and self.S.shape[0] == self.n and self.S.shape[-1] == self.X.shape[1]
+        self.ops = ops if (ops is not None and per_point) else None
 
     def __len__(self):
         if self.drop_last:
@@ -67,6 +70,9 @@ class DeviceBatches:
             hi = min(lo + self.batch_size, self.n)
             if self.shuffle:
                 idx = perm[lo:hi]
-                yield self.X.index_select(0, idx), self.S.index_select(0, idx)
+                if self.ops is not None:
+                    yield self.ops.gather_points(self.X, self.S, idx)
+                else:
+                    yield self.X.index_select(0, idx), self.S.index_select(0, idx)
             else:
                 yield self.X[lo:hi], self.S[lo:hi]

@@ -311,9 +311,9 @@ class OnlineDeconvGMM(DeconvGMM):
 
     def fit(self, data, val_data=None, verbose=False, interval=1, init=True):
         X, S, layout = self._prep(data)
-        loader = DeviceBatches((X, S), self.batch_size, self.device, shuffle=True, drop_last=True)
+        loader = DeviceBatches((X, S), self.batch_size, self.device, shuffle=True, drop_last=True, ops=_ops)
         if init:
-            init_loader = DeviceBatches((X, S), self.k_means_factor * self.batch_size, self.device, shuffle=True)
+            init_loader = DeviceBatches((X, S), self.k_means_factor * self.batch_size, self.device, shuffle=True, ops=_ops)
             self._init_sum_stats(init_loader, X.shape[0])
         elif not hasattr(self, "sum_resps"):
             self._reset_running_sums()
@@ -385,7 +385,7 @@ class BatchDeconvGMM(OnlineDeconvGMM):
         X, S, layout = self._prep(data)
         n_total = _global_count(X.shape[0], self.device)
         if init:
-            init_loader = DeviceBatches((X, S), self.k_means_factor * self.batch_size, self.device, shuffle=True)
+            init_loader = DeviceBatches((X, S), self.k_means_factor * self.batch_size, self.device, shuffle=True, ops=_ops)
             self._init_sum_stats(init_loader, X.shape[0])
         self.train_ll_curve = []
         if val_data:
@@ -597,7 +597,7 @@ class BaseSGDGMM:
 
     def _batches(self, data, shuffle):
         X, S = as_tensors(data)
-        return DeviceBatches((X, S), self.batch_size, self.device, shuffle=shuffle and self.shuffle)
+        return DeviceBatches((X, S), self.batch_size, self.device, shuffle=shuffle and self.shuffle, ops=_ops)
 
     # ---- fused optimiser step: no autograd graph, five launches per minibatch -------------------
     fused_step = True   # False: the autograd route (module.log_prob_sum -> loss.backward -> optimiser.step)

@@ -469,3 +469,30 @@ def posterior_logprob(X, S, log_alpha, mu, Sigma, V, noise="full"):
                                                    _ptr(status), _ptr(ws), ws.numel(), _stream(dev))
     check(rc, "dgmm_posterior_logprob_f32")
     return out, status
+
+
+def gather_points(X, S, idx, outX=None, outS=None):
+    """Rows ``idx`` (int64, on the device) of ``X [N,D]`` and of the noise table ``S`` (``[N,D,D]``, ``[N,D]``
+    or None) as contiguous batch tensors, in one launch (the device-resident DataLoader)."""
+    X = _f32c(X, "X")
+    dev = X.device
+    N, D = X.shape
+    if idx.dtype != torch.int64 or not idx.is_cuda or not idx.is_contiguous():
+        raise DgmmError("idx must be a contiguous int64 CUDA tensor")
+    B = idx.numel()
+    if S is None:
+        code = _lib.NOISE_NONE
+    else:
+        S = _f32c(S, "noise_covars", dev)
+        code = _lib.NOISE_FULL if S.dim() == 3 else _lib.NOISE_DIAG
+        if S.shape[0] != N or tuple(S.shape[1:]) not in ((D, D), (D,)):
+            raise ValueError("noise_covars has shape %s for X %s" % (tuple(S.shape), tuple(X.shape)))
+    if outX is None:
+        outX = torch.empty(B, D, dtype=torch.float32, device=dev)
+    if outS is None and S is not None:
+        outS = torch.empty((B,) + tuple(S.shape[1:]), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dgmm_gather_points_f32(_ptr(X), _ptr(S), code, _ptr(idx), B, D, _ptr(outX), _ptr(outS),
+                                               _stream(dev))
+    check(rc, "dgmm_gather_points_f32")
+    return outX, outS

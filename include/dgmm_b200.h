@@ -212,6 +212,15 @@ DGMM_API int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, con
 DGMM_API int dgmm_kmeans_update_f32(int mode, const float* stats, int D, int K, float* centroids,
                                     float* counts_run, void* stream);
 
+/* ---- device-resident minibatches --------------------------------------------------------- */
+
+/* Gathers the rows idx[0..B) (int64, device) of X [N,D] and of the noise table (DGMM_NOISE_FULL: [N,D,D],
+ * DGMM_NOISE_DIAG: [N,D], DGMM_NOISE_NONE: nothing) into contiguous outX [B,D] / outS [B,...] in one launch.
+ * Replaces the DataLoader's per-sample __getitem__ + collate (deconv/gmm/data.py:7-17,
+ * deconv/gmm/sgd_gmm.py:139-145, deconv/gmm/online_deconv_gmm.py:43-56) for tables resident on the GPU. */
+DGMM_API int dgmm_gather_points_f32(const float* X, const float* S, int noise_layout, const int64_t* idx, int64_t B,
+                                    int D, float* outX, float* outS, void* stream);
+
 /* ---- posterior sampling (device pointers) ------------------------------------------------ */
 
 /* M draws per point from the posterior mixture p(v | w_i, S_i) = sum_j r_ij N(b_ij, B_ij) without

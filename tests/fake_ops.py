@@ -221,3 +221,7 @@ def posterior_logprob(X, S, log_alpha, mu, Sigma, V, noise="full"):
     Sn = _full_noise(X, S, noise)
     out = orc.posterior_log_prob(_np(X), Sn, np.exp(_np(log_alpha)), _np(mu), _np(Sigma), _np(V))
     return torch.tensor(out, dtype=torch.float32, device=X.device), torch.zeros(1, dtype=torch.int32, device=X.device)
+
+
+def gather_points(X, S, idx, outX=None, outS=None):
+    return X.index_select(0, idx), (S.index_select(0, idx) if S is not None else None)

@@ -179,3 +179,41 @@ def test_assign_rejects_cpu_tensors():
     from density_deconvolution_b200 import ops
     with pytest.raises(Exception):
         ops.kmeans_assign(torch.zeros(4, 2), torch.zeros(2, 2))
+
+
+# ---- device-resident minibatch gather (dgmm_gather_points_f32) --------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,layout", [(1, "full"), (3, "full"), (9, "full"), (10, "full"), (16, "full"), (32, "full"),
+                                      (10, "diag"), (7, "diag"), (10, "none")])
+def test_gather_points_is_exact(D, layout):
+    from density_deconvolution_b200 import ops
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev).manual_seed(D)
+    N, B = 5000, 1237
+    X = torch.randn(N, D, device=dev, generator=g)
+    S = {"full": torch.randn(N, D, D, device=dev, generator=g), "diag": torch.rand(N, D, device=dev, generator=g),
+         "none": None}[layout]
+    idx = torch.randperm(N, device=dev, generator=g)[:B].contiguous()
+    bx, bs = ops.gather_points(X, S, idx)
+    assert torch.equal(bx, X.index_select(0, idx))
+    if S is None:
+        assert bs is None
+    else:
+        assert torch.equal(bs, S.index_select(0, idx))
+    bx0, _ = ops.gather_points(X, S, idx[:0].contiguous())
+    assert bx0.shape == (0, D)
+
+
+@pytest.mark.gpu
+def test_device_batches_cover_the_table_once_per_epoch():
+    from density_deconvolution_b200 import ops
+    from density_deconvolution_b200.data import DeviceBatches
+    dev = torch.device("cuda", 0)
+    N, D = 1000, 4
+    X = torch.arange(N, device=dev, dtype=torch.float32)[:, None].repeat(1, D)
+    S = X[:, :, None] * torch.eye(D, device=dev)
+    loader = DeviceBatches((X, S), 96, dev, shuffle=True, ops=ops)
+    seen = torch.cat([xb[:, 0] for xb, sb in loader])
+    assert len(loader) == 11 and torch.equal(seen.sort()[0], X[:, 0])
+    for xb, sb in loader:
+        assert torch.equal(sb[:, 0, 0], xb[:, 0])          # the noise rows travel with their points
