@@ -143,7 +143,7 @@ namespace unrolled {
 }  // namespace dgmm
 #undef DGMM_LOOP
 
-#define DGMM_LOOP _Pragma("unroll 1")
+#define DGMM_LOOP _Pragma("unroll 4")
 namespace dgmm {
 namespace rolled {
 #include "dgmm_core_body.inc"

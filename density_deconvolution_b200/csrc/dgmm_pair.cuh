@@ -227,7 +227,7 @@ namespace unrolled {
 }  // namespace dgmm
 #undef DGMM_LOOP
 
-#define DGMM_LOOP _Pragma("unroll 1")
+#define DGMM_LOOP _Pragma("unroll 4")
 namespace dgmm {
 namespace rolled {
 #include "dgmm_pair_body.inc"
