@@ -150,7 +150,7 @@ def run_reference(args, wl):
                 cpu_baseline=dict(value=value, unit=UNIT, cores=cores, kind="port", sample=sample),
                 e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # -----------------------------------------------------------------------------------------
@@ -367,7 +367,7 @@ def run_b200(args, wl):
         sgd=sgd, clocks=clocks, roofline=roofline, e2e=e2e)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(wl)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -469,8 +469,24 @@ def run_e2e(args, wl, ops, dist, dev, world, X, S, fresh, n_total, w_reg, barrie
                     "pinned host buffers, 262144-point chunks, copy/compute overlap on two streams")
 
 
+_JSON_OUT = None
+
+
+def emit(line):
+    """The one JSON line of the contract, on the process's ORIGINAL stdout."""
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
     args = parse_args()
+    # stdout carries exactly one JSON line: everything else written to fd 1 by this process or the libraries it
+    # loads (NCCL's version banner, extension build chatter) is sent to stderr instead
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     wl = dict(WORKLOADS[args.workload])
     if args.points:
         wl["N"] = args.points
