@@ -485,6 +485,14 @@ int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int no
             ok = v.fn && fit_geometry(dev, v, mode, D, noise, has_g, &p);
         }
     }
+    if (ok && which == 0 && D > 16 && v.sigp == ST_SMEM && t.rc < 0 && 2 * (p.smem + 1024) > (size_t)dev.smem_optin) {
+        // D = 17..24: Sigma_j columns in shared memory leave room for one block per SM only
+        Plan q = p;
+        const PairVariant alt = kDims[D].pair(mode, 1, p.gcls, nz);
+        if (alt.fn && fit_geometry(dev, alt, mode, D, noise, has_g, &q) && 2 * (q.smem + 1024) <= (size_t)dev.smem_optin) {
+            v = alt; p = q; which = 1;
+        }
+    }
     if (!ok) {
         which = 2;
         v = kDims[D].pair(mode, 2, GCLS_ANY, NZ_ANY);

@@ -32,6 +32,36 @@ inline PairVariant pair_variant() {
     return v;
 }
 
+// D = 17..DGMM_PAIR_UNROLL_D: the fully unrolled body still fits 255 registers with a few spilled words
+// (ptxas: <= 480 bytes of stack at D = 20), which is an order of magnitude faster than the rolled fallback.
+// Compiled only for the group class of K = 64..128 (one block of 128 threads per SM) to keep build time down.
+#ifndef DGMM_PAIR_UNROLL_D
+#define DGMM_PAIR_UNROLL_D 24
+#endif
+template <int D, int MODE, int SIGP, int ACCP, int GCLS, int NZ>
+inline PairVariant pair_variant_wide_unrolled() {
+    PairVariant v;
+    v.fn = reinterpret_cast<const void*>(&unrolled::pair_kernel<D, MODE, SIGP, ACCP, GCLS, NZ, kPairMaxThreads, 1>);
+    v.sigp = SIGP; v.accp = ACCP; v.gcls = GCLS; v.nz = NZ; v.max_threads = kPairMaxThreads; v.min_blocks = 1;
+    return v;
+}
+// K = 64..128: Sigma_j in shared-memory columns; K = 129..256 (one 256-thread group): the columns no longer
+// fit beside the ring, Sigma_j is read through L1 instead.
+template <int D, int MODE, int ACCP>
+inline PairVariant pair_wide_unrolled(int gcls, int nz, bool sigma_global = false) {
+    if (gcls == GCLS_MW4 && sigma_global) {
+        if (nz == NZ_FULL) return pair_variant_wide_unrolled<D, MODE, ST_GLOBAL, ACCP, GCLS_MW4, NZ_FULL>();
+        if (nz == NZ_DIAG) return pair_variant_wide_unrolled<D, MODE, ST_GLOBAL, ACCP, GCLS_MW4, NZ_DIAG>();
+    } else if (gcls == GCLS_MW4) {
+        if (nz == NZ_FULL) return pair_variant_wide_unrolled<D, MODE, ST_SMEM, ACCP, GCLS_MW4, NZ_FULL>();
+        if (nz == NZ_DIAG) return pair_variant_wide_unrolled<D, MODE, ST_SMEM, ACCP, GCLS_MW4, NZ_DIAG>();
+    } else if (gcls == GCLS_MWN) {
+        if (nz == NZ_FULL) return pair_variant_wide_unrolled<D, MODE, ST_GLOBAL, ACCP, GCLS_MWN, NZ_FULL>();
+        if (nz == NZ_DIAG) return pair_variant_wide_unrolled<D, MODE, ST_GLOBAL, ACCP, GCLS_MWN, NZ_DIAG>();
+    }
+    return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
+}
+
 // The four group classes of one placement.  Groups wider than 128 lanes (GCLS_MWN) need blocks of
 // 256 threads, so that class is always compiled with the (256, 1) bounds.
 template <int D, int MODE, int SIGP, int ACCP, int NZ, int MAXT, int MINB>
@@ -59,7 +89,9 @@ inline PairVariant pair_by_gcls(int gcls, int nz) {
 //   13 <= D <= 16: Sigma_j in shared-memory columns, accumulators in tensor memory, 255 registers,
 //                  2 blocks/SM       [D=16,K=128: 0.61 vs 0.44 with shared-memory accumulators]
 //   LOGLIK       : Sigma_j in shared-memory columns; 128 registers x 4 blocks/SM (D <= 12), 255 above
-//   D > 16       : fallback only (rolled loops, local-memory arrays)
+//   D = 17..24   : K >= 64: as 13..16 (unrolled, a few spilled words; Sigma_j through L1 when its columns
+//                  would leave one block per SM, and for K > 128); otherwise the fallback
+//   D > 24       : fallback only (rolled loops, local-memory arrays)
 template <int D>
 inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
     if (which == 2) {
@@ -70,6 +102,11 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
     if (which == 1) {  // alternative placements (tuning sweeps, tools/gpu_ab.sh)
         if constexpr (D <= 12) {
             if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 4>(gcls, nz);
+        } else if constexpr (D > DGMM_UNROLL_D && D <= DGMM_PAIR_UNROLL_D) {
+            // Sigma_j through L1 instead of shared-memory columns: the planner takes this one when the
+            // columns would leave room for only one block per SM (two blocks of 4 warps beat one)
+            if (mode == MODE_LOGLIK) return pair_wide_unrolled<D, MODE_LOGLIK, ST_GLOBAL>(gcls, nz, true);
+            if constexpr (D <= 20) return pair_wide_unrolled<D, MODE_STATS, ST_TMEM>(gcls, nz, true);
         }
         return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
     }
@@ -88,6 +125,9 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
         if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, kPairMaxThreads, 1>(gcls, nz);
         if (gcls != GCLS_SUB) return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_TMEM, kPairMaxThreads, 1>(gcls, nz);
         return pair_by_gcls<D, MODE_STATS, ST_GLOBAL, ST_SMEM, kPairMaxThreads, 1>(gcls, nz);
+    } else if constexpr (D <= DGMM_PAIR_UNROLL_D) {
+        if (mode == MODE_LOGLIK) return pair_wide_unrolled<D, MODE_LOGLIK, ST_GLOBAL>(gcls, nz);
+        return pair_wide_unrolled<D, MODE_STATS, ST_TMEM>(gcls, nz);
     }
     return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
 }

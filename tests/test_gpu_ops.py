@@ -81,6 +81,18 @@ def test_dims_rolled(ops, D):
     run_case(ops, N=67, D=D, K=4, seed=200 + D)
 
 
+@pytest.mark.parametrize("D,K,noise", [(17, 64, "full"), (18, 128, "diag"), (19, 100, "full"), (20, 128, "full"),
+                                       (20, 64, "diag"), (17, 128, "diag"), (20, 256, "full"), (19, 200, "diag"),
+                                       (21, 64, "full"), (22, 128, "diag"), (23, 100, "full"), (24, 128, "full"),
+                                       (24, 64, "diag")])
+def test_dims_unrolled_with_spills(ops, D, K, noise):
+    """D = 17..24 with 64+ components: the fully unrolled kernels (main placement, not the rolled fallback)."""
+    for mode in (0, 1):
+        plan = ops.get_plan(mode, D, K, 1000, noise=noise)
+        assert plan["rc"] in (0, 1), plan   # not the rolled fallback (rc == 2)
+    run_case(ops, N=203 if K <= 128 else 75, D=D, K=K, seed=250 + D + K, noise=noise, with_g=(D % 2 == 0))
+
+
 @pytest.mark.parametrize("K", [1, 2, 3, 8, 10, 31, 32, 33, 64, 100, 128, 256])
 def test_component_counts(ops, K):
     run_case(ops, N=257 if K <= 64 else 96, D=4, K=K, seed=300 + K)
