@@ -2,22 +2,28 @@
 """Benchmark of the deconvolution-GMM hot path (BASELINE.json metric:
 "(point,component) log-lik evals/sec and EM iters/sec").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c5|small] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c2|c3|c4|small]
+                    [--secondary c2,c3,c4|none] [--impl reference]
 
 A STEP is one full EM iteration over the rank's resident shard: the fused statistics kernel
 (log-likelihood + E-step + M-step reductions for every (point, component) pair), the all-reduce
 of the packed statistics (N > 1) and the closed-form parameter update.  ``value`` is
 (point, component) evaluations per second over the whole job inside those steps;
-``em_iters_per_sec`` and the log-likelihood-only pass are reported beside it.
+``em_iters_per_sec``, the log-likelihood-only pass and the minibatch-SGD step are reported beside it.
 
 Workloads (per GPU; weak scaling, every rank generates its own shard on the device):
-  c2    synthetic N=1e7,   D=10, K=64,  full per-point noise   (BASELINE.json configs[1], default)
-  c3    wine-shaped N=1.25e7, D=9,  K=128 (configs[2]: 1e8 points over 8 GPUs)
-  c5    synthetic N=1.25e7, D=16, K=128 (configs[4]: 1e8 points over 8 GPUs, headline shape)
+  c5    synthetic N=1.25e7, D=16, K=128 full noise: BASELINE.json configs[4], the north_star headline
+        (exactly N=1e8 at 8 GPUs) -- the DEFAULT: ``value`` / ``roofline`` / ``e2e`` are this workload's
+  c2    synthetic N=1e7, D=10, K=64 full noise (configs[1])
+  c3    wine table (6497x9, tests/golden) tiled to N=1.25e7 with fresh per-point noise, K=128 (configs[2])
+  c4    ionosphere table (351x32, tests/golden) tiled x1024 with fresh per-point noise, K=256 (configs[3])
   small N=1e6, D=10, K=64 (quick check)
+The workloads named by --secondary are measured after the headline one (fewer steps, no end-to-end arm)
+and reported under ``secondary`` in the same JSON line, each with its own roofline block.
 
-The ``--impl reference`` arm and the ``cpu_baseline`` object time a torch-CPU port of the
-reference's own E-step/M-step call sequence (oracle/torch_port.py) on the host cores.
+The ``--impl reference`` arm and the ``cpu_baseline`` object time the reference's CPU path on the host cores:
+the UNMODIFIED reference staged under baseline/_ref (kind "reference") when present, else the torch-CPU port of
+its call sequence (oracle/torch_port.py, kind "port").
 """
 import argparse
 import json
@@ -32,9 +38,12 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 WORKLOADS = {
-    "c2": dict(N=10_000_000, D=10, K=64, noise="full", name="synthetic N=1e7/GPU D=10 K=64 full per-point noise"),
-    "c3": dict(N=12_500_000, D=9, K=128, noise="full", name="wine-shaped N=1.25e7/GPU D=9 K=128 full noise"),
-    "c5": dict(N=12_500_000, D=16, K=128, noise="full", name="synthetic N=1.25e7/GPU D=16 K=128 full noise"),
+    "c5": dict(N=12_500_000, D=16, K=128, noise="full", name="synthetic N=1.25e7/GPU D=16 K=128 full noise (configs[4])"),
+    "c2": dict(N=10_000_000, D=10, K=64, noise="full", name="synthetic N=1e7/GPU D=10 K=64 full per-point noise (configs[1])"),
+    "c3": dict(N=12_500_000, D=9, K=128, noise="full", table="ref_wine_k128_f64.npz", table_iter=20,
+               name="wine table (6497x9) tiled to N=1.25e7/GPU, fresh per-point full noise, K=128 (configs[2])"),
+    "c4": dict(N=351 * 1024, D=32, K=256, noise="full", table="ref_ionosphere_k256_f64.npz", table_iter=5,
+               name="ionosphere table (351x32) tiled x1024 per GPU, fresh per-point full noise, K=256 (configs[3])"),
     "small": dict(N=1_000_000, D=10, K=64, noise="full", name="synthetic N=1e6/GPU D=10 K=64 full noise"),
 }
 METRIC = "pair_loglik_evals_per_sec"
@@ -66,8 +75,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--points", type=int, default=0, help="override points per GPU")
+    ap.add_argument("--workload", default="c5", choices=sorted(WORKLOADS))
+    ap.add_argument("--secondary", default="c2,c3,c4", help="comma list of further workloads, or 'none'")
+    ap.add_argument("--points", type=int, default=0, help="override points per GPU (headline workload)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-sgd", action="store_true")
@@ -76,7 +86,7 @@ def parse_args():
 
 
 # -----------------------------------------------------------------------------------------
-# CPU arm: torch port of the reference on the host cores
+# CPU arm: the reference's own E-step + M-step (baseline/_ref) or its torch port, on the host cores
 # -----------------------------------------------------------------------------------------
 def cpu_problem(wl, n, seed=99):
     import torch
@@ -88,66 +98,120 @@ def cpu_problem(wl, n, seed=99):
     return X, S, alpha, mu0, Sigma * 1.2
 
 
-def cpu_em_rate(wl, n, reps=1):
-    """(pairs/s, seconds per iteration) of the reference port's EM iteration on ``n`` points."""
+def reference_available():
+    return os.path.isfile(os.path.join(ROOT, "baseline", "_ref", "deconv", "gmm", "deconv_gmm.py"))
+
+
+class CpuArm:
+    """One EM iteration on the host cores over ``n`` points, chunked so that the reference's
+    ``[B,K,D,D]`` temporaries stay bounded (the way BatchDeconvGMM accumulates, batch_deconv_gmm.py:44-75)."""
+
+    def __init__(self, wl):
+        import torch
+        self.wl = wl
+        self.torch = torch
+        self.kind = "reference" if reference_available() else "port"
+        K, D = wl["K"], wl["D"]
+        self.chunk = max(256, min(4096, (1 << 28) // (K * D * D * 4 * 8)))
+        if self.kind == "reference":
+            sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref"))
+            import warnings
+            warnings.filterwarnings("ignore")
+            from deconv.gmm.batch_deconv_gmm import BatchDeconvGMM      # the UNMODIFIED reference
+            self.model = BatchDeconvGMM(K, D, w=1e-3, batch_size=self.chunk)
+            self.what = ("the UNMODIFIED reference staged under baseline/_ref: BatchDeconvGMM._step_1 / _step_2 "
+                         "(each DeconvGMM._e_step, deconv/gmm/deconv_gmm.py:39-79) over chunks of %d points + the update of "
+                         "batch_deconv_gmm.py:65-75" % self.chunk)
+        else:
+            from oracle import torch_port as tp
+            self.tp = tp
+            self.what = ("torch-CPU port of deconv/gmm/deconv_gmm.py:39-109 (oracle/torch_port.py), chunks of %d points"
+                         % self.chunk)
+
+    def set_params(self, alpha, mu, Sigma):
+        self.alpha, self.mu, self.Sigma = alpha.clone(), mu.clone(), Sigma.clone()
+
+    def em_iteration(self, X, S):
+        torch = self.torch
+        if self.kind == "port":
+            _, w, self.mu, self.Sigma = self.tp.em_iteration_single_pass(X, S, self.alpha.reshape(-1), self.mu,
+                                                                          self.Sigma, 1e-3, chunk=self.chunk)
+            self.alpha = w.reshape(-1)
+            return
+        m = self.model
+        K, D = self.wl["K"], self.wl["D"]
+        m.weights, m.means, m.covars = self.alpha.reshape(K, 1), self.mu, self.Sigma
+        n = X.shape[0]
+        sr, sm = torch.zeros(K, 1), torch.zeros(K, D)
+        for lo in range(0, n, self.chunk):                            # batch_deconv_gmm.py:48-55
+            _, (a, b) = m._step_1((X[lo:lo + self.chunk], S[lo:lo + self.chunk]))
+            sr += a
+            sm += b
+        new_means = sm / sr
+        sc = torch.zeros(K, D, D)
+        for lo in range(0, n, self.chunk):                            # :58-63
+            sc += m._step_2((X[lo:lo + self.chunk], S[lo:lo + self.chunk]), new_means)
+        self.alpha = (sr / n).reshape(-1)                             # :65-75
+        self.mu = new_means
+        self.Sigma = (sc + 2 * m.w) / sr[:, :, None]
+
+
+def cpu_rate(arm, wl, n, reps=1, params=None):
     import torch
-    from oracle import torch_port as tp
     X, S, alpha, mu, Sigma = cpu_problem(wl, n)
-    chunk = max(256, min(4096, (1 << 28) // (wl["K"] * wl["D"] * wl["D"] * 4 * 8)))
     best = float("inf")
     for _ in range(reps):
+        arm.set_params(alpha, mu, Sigma)
         t0 = time.perf_counter()
-        tp.em_iteration_single_pass(X, S, alpha, mu, Sigma, 1e-3, chunk=chunk)
+        arm.em_iteration(X, S)
         best = min(best, time.perf_counter() - t0)
-    return n * wl["K"] / best, best, chunk
+    return n * wl["K"] / best, best
 
 
 def cpu_baseline(wl, budget_s=15.0):
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    rate, _, chunk = cpu_em_rate(wl, 2048)                       # warm-up + speed estimate
-    n = int(min(131072, max(4096, rate * budget_s / wl["K"])))
+    arm = CpuArm(wl)
+    rate, _ = cpu_rate(arm, wl, 1024)                       # warm-up + speed estimate
+    n = int(min(131072, max(2048, rate * budget_s / wl["K"])))
     n = (n // 1024) * 1024
-    rate, secs, chunk = cpu_em_rate(wl, n)
-    return dict(value=rate, unit=UNIT, cores=cores, kind="port",
-                sample="one EM iteration (E-step + M-step, torch-CPU port of deconv/gmm/deconv_gmm.py:39-109, "
-                       "float32, %d torch threads, chunks of %d points) on %d points of the same workload: %.1f s"
-                       % (torch.get_num_threads(), chunk, n, secs))
+    rate, secs = cpu_rate(arm, wl, n)
+    return dict(value=rate, unit=UNIT, cores=cores, kind=arm.kind,
+                sample="one EM iteration (E-step + M-step) of %s, float32, %d torch threads, on %d points of the "
+                       "same workload: %.1f s" % (arm.what, torch.get_num_threads(), n, secs))
 
 
 def run_reference(args, wl):
-    """``--impl reference``: the reference's CPU path (torch port) on the host cores."""
+    """``--impl reference``: the reference's CPU path on the host cores."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    rate, _, _ = cpu_em_rate(wl, 1024)
+    arm = CpuArm(wl)
+    rate, _ = cpu_rate(arm, wl, 1024)
     # each step: a bounded sample sized for ~3 s so that K+W steps end within a few minutes
     n = int(min(65536, max(1024, rate * 3.0 / wl["K"])))
     n = (n // 512) * 512
-    from oracle import torch_port as tp
     X, S, alpha, mu, Sigma = cpu_problem(wl, n)
-    chunk = max(256, min(4096, (1 << 28) // (wl["K"] * wl["D"] * wl["D"] * 4 * 8)))
-    w = alpha[:, None]
+    arm.set_params(alpha, mu, Sigma)
     for _ in range(args.warmup):
-        _, w, mu, Sigma = tp.em_iteration_single_pass(X, S, w.reshape(-1), mu, Sigma, 1e-3, chunk=chunk)
-        w = w
+        arm.em_iteration(X, S)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        _, w, mu, Sigma = tp.em_iteration_single_pass(X, S, w.reshape(-1), mu, Sigma, 1e-3, chunk=chunk)
+        arm.em_iteration(X, S)
     dt = time.perf_counter() - t0
     value = n * wl["K"] * args.steps / dt
-    sample = ("each step = one EM iteration of the torch-CPU port of the reference (oracle/torch_port.py) on a "
-              "%d-point sample of the workload, float32, %d torch threads" % (n, torch.get_num_threads()))
+    sample = ("each step = one EM iteration of %s on a %d-point sample of the workload, float32, %d torch threads"
+              % (arm.what, n, torch.get_num_threads()))
     line = dict(impl="reference", metric=METRIC, value=value, unit=UNIT, n_gpus=args.gpus, steps=args.steps,
                 warmup=args.warmup, ms_per_step=dt / args.steps * 1e3, higher_is_better=True, scaling="weak",
                 vs_baseline=None, dtype="f32", data="synthetic",
                 config=dict(workload=wl["name"], D=wl["D"], K=wl["K"], sample_points=n),
                 em_iters_per_sec_full_workload=value / (wl["N"] * wl["K"]),
-                cpu_baseline=dict(value=value, unit=UNIT, cores=cores, kind="port", sample=sample),
+                cpu_baseline=dict(value=value, unit=UNIT, cores=cores, kind=arm.kind, sample=sample),
                 e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
     emit(line)
@@ -201,33 +265,70 @@ class ClockSampler:
 
 
 # -----------------------------------------------------------------------------------------
-# GPU arm
+# workload data
 # -----------------------------------------------------------------------------------------
-def run_b200(args, wl):
+def tril_unpack(P, D):
+    import numpy as np
+    ia, ib = np.tril_indices(D)
+    C = np.zeros(P.shape[:-1] + (D, D), dtype=np.float64)
+    C[..., ia, ib] = P
+    C[..., ib, ia] = P
+    return C
+
+
+def make_workload(wl, N, dev, rank):
+    """``(X, S, alpha, mu0, Sigma0)`` on the device.  Synthetic workloads: the reference's generator
+    (density_deconvolution_b200/synthetic.py); table workloads: the real table of tests/golden tiled to N points, every
+    copy with its own per-point full-noise draw (added to the point), parameters = the reference's fit after
+    ``table_iter`` EM iterations."""
+    import numpy as np
     import torch
-    import torch.distributed as dist
-    from density_deconvolution_b200 import ops
     from density_deconvolution_b200.synthetic import make_mixture, make_points
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device (the B200 path has no CPU fallback; use --impl reference)")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    if world != args.gpus and rank == 0:
-        print("bench.py: WORLD_SIZE=%d but --gpus %d; using WORLD_SIZE" % (world, args.gpus), file=sys.stderr)
-
-    N, D, K = (args.points or wl["N"]), wl["D"], wl["K"]
+    D, K = wl["D"], wl["K"]
+    path = os.path.join(ROOT, "tests", "golden", wl.get("table", "-"))
+    if "table" in wl and os.path.isfile(path):
+        g = np.load(path)
+        X0 = torch.tensor(g["X64"], dtype=torch.float32, device=dev)
+        it = wl["table_iter"]
+        alpha = torch.tensor(g["it%d_weights" % it], dtype=torch.float32, device=dev)
+        mu = torch.tensor(g["it%d_means" % it], dtype=torch.float32, device=dev)
+        Sigma = torch.tensor(tril_unpack(g["it%d_covars_tril" % it].astype(np.float64), D), dtype=torch.float32, device=dev)
+        gen = torch.Generator(device=dev).manual_seed(4321 + rank)
+        X = torch.empty(N, D, device=dev)
+        S = torch.empty(N, D, D, device=dev)
+        n0 = X0.shape[0]
+        chunk = 1 << 19
+        for lo in range(0, N, chunk):
+            n = min(chunk, N - lo)
+            idx = (torch.arange(lo, lo + n, device=dev) % n0)
+            Q = (0.5 / D ** 0.5) * torch.randn(n, D, D, device=dev, generator=gen)
+            S[lo:lo + n] = Q.transpose(1, 2) @ Q
+            S[lo:lo + n].diagonal(dim1=1, dim2=2).add_(1e-3)
+            e = torch.randn(n, 1, D, device=dev, generator=gen)
+            X[lo:lo + n] = X0[idx] + (e @ Q)[:, 0, :] + (1e-3 ** 0.5) * torch.randn(n, D, device=dev, generator=gen)
+            del Q
+        return X, S, alpha / alpha.sum(), mu, Sigma.contiguous(), "table"
     alpha, mu_true, Sigma_true, q = make_mixture(D, K, seed=0, device=dev)
     X, S = make_points(N, alpha, mu_true, q, seed=1234 + rank, noise=wl["noise"])
     del q
     g = torch.Generator(device="cpu").manual_seed(7)
     mu0 = (mu_true.cpu() + 0.3 * torch.randn(K, D, generator=g)).to(dev)
-    Sigma0 = (1.2 * Sigma_true).contiguous()
+    return X, S, alpha, mu0, (1.2 * Sigma_true).contiguous(), "synthetic"
+
+
+# -----------------------------------------------------------------------------------------
+# GPU arm
+# -----------------------------------------------------------------------------------------
+class Env:
+    pass
+
+
+def measure(env, args, key, wl, N, steps, warmup, do_sgd, do_e2e):
+    """EM iteration, log-likelihood pass, SGD step (and the end-to-end arm) of one workload."""
+    import torch
+    ops, dist, dev, world, rank = env.ops, env.dist, env.dev, env.world, env.rank
+    D, K = wl["D"], wl["K"]
+    X, S, alpha, mu0, Sigma0, data_kind = make_workload(wl, N, dev, rank)
 
     def fresh():
         a = alpha.clone()
@@ -248,26 +349,125 @@ def run_b200(args, wl):
         a, la, m, Sg = p
         ops.loglik(X, S, la, m, Sg, noise=wl["noise"])
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, params, steps):
-        barrier()
+    def timed(fn, params, nsteps):
+        env.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record()
-        for _ in range(steps):
+        for _ in range(nsteps):
             fn(params)
         e1.record()
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-        barrier()
+        env.barrier()
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms.item() * 1e-3, (t0, t1)
+
+    # ---- the timed region: `steps` EM iterations --------------------------------------------
+    params = fresh()
+    for _ in range(warmup):
+        em_step(params)
+    ops.pair_timing(True)
+    t_em, window = timed(em_step, params, steps)
+    pair_ms = ops.pair_times()
+    ops.pair_timing(False)
+    ll_after = (stats[-4] + stats[-3]).item() / n_total
+    nonpd = stats[-1].item()
+
+    # ---- log-likelihood-only pass (score_batch), same protocol ------------------------------
+    for _ in range(3):
+        ll_step(params)
+    ops.pair_timing(True)
+    t_ll, _ = timed(ll_step, params, steps)
+    pair_ms_ll = ops.pair_times()
+    ops.pair_timing(False)
+
+    sgd = run_sgd(args, env, wl, X, S, fresh) if do_sgd else None
+    e2e = run_e2e(args, env, wl, X, S, fresh, n_total, w_reg, steps) if do_e2e else None
+
+    pairs_per_step = float(n_total) * K
+    pair_avg_s = (sum(pair_ms) / len(pair_ms)) * 1e-3
+    pair_ll_avg_s = (sum(pair_ms_ll) / len(pair_ms_ll)) * 1e-3
+    bytes_per_point = 4 * (D + (D * D if wl["noise"] == "full" else D))
+    plan = ops.get_plan(1, D, K, N, noise=wl["noise"])
+    team = plan["rc"] == 3
+    kname = "team_loglik_kernel + team_stats_kernel (two passes)" if team else "pair_kernel<MODE_STATS>"
+    kname_ll = "team_loglik_kernel" if team else "pair_kernel<MODE_LOGLIK>"
+    fp32_peak = env.fp32_peak
+    roofline = dict(
+        bound="fp32", kernel=kname,
+        achieved=N * K * F_em(D) / pair_avg_s / 1e12, peak=fp32_peak / 1e12, unit="TFLOP/s",
+        frac=N * K * F_em(D) / pair_avg_s / fp32_peak,
+        peak_source="in-bench register-only FFMA probe on this GPU (MEASURED_PEAKS.json has no FP32 entry; "
+                    "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)",
+        frac_of_nominal=N * K * F_em(D) / pair_avg_s / 74.4e12,
+        flops_per_pair=F_em(D), pairs_per_launch=N * K, launch_ms=pair_avg_s * 1e3,
+        share_of_step=pair_avg_s * steps / t_em if world == 1 else None,
+        traffic=ncu_traffic(key, "pair_kernel<MODE_STATS>") if N == wl["N"] else None,
+        traffic_note="DRAM bytes per launch from the committed ncu --set full capture (profiles/ncu_traffic.json); "
+                     "algorithmic bytes per launch = %d" % (N * bytes_per_point),
+        hbm=dict(achieved=N * bytes_per_point / pair_avg_s / 1e9, peak=env.hbm_peak, unit="GB/s",
+                 frac=N * bytes_per_point / pair_avg_s / 1e9 / env.hbm_peak, peak_source=env.hbm_source),
+        loglik_kernel=dict(kernel=kname_ll, launch_ms=pair_ll_avg_s * 1e3,
+                           achieved=N * K * F_ll(D) / pair_ll_avg_s / 1e12,
+                           frac=N * K * F_ll(D) / pair_ll_avg_s / fp32_peak,
+                           frac_of_nominal=N * K * F_ll(D) / pair_ll_avg_s / 74.4e12, flops_per_pair=F_ll(D)))
+    if sgd:
+        B = sgd["batch_per_gpu"]
+        sgd["roofline_frac"] = B * K * F_em(D) / (sgd["ms_per_step"] * 1e-3) / fp32_peak
+        sgd["roofline_note"] = "batch_per_gpu x K x F_em(D) / step time / FP32 peak (whole step: gather, statistics, " \
+                               "all-reduce, Adam)"
+    launches = 5 if team else 4
+    res = dict(
+        workload=wl["name"], data=data_kind, points_per_gpu=N, points_total=n_total, D=D, K=K, noise=wl["noise"],
+        value=pairs_per_step * steps / t_em, unit=UNIT, steps=steps, warmup=warmup, ms_per_step=t_em / steps * 1e3,
+        em_iters_per_sec=steps / t_em,
+        loglik_only=dict(value=pairs_per_step * steps / t_ll, unit=UNIT, ms_per_pass=t_ll / steps * 1e3),
+        mean_loglik_after=ll_after, nonpd_pairs=nonpd, launch_plan=plan,
+        gpu_launches=launches * steps,
+        gpu_launches_note="per step: prepare, %s, finalize, mstep_kernel" % kname,
+        sgd=sgd, roofline=roofline, e2e=e2e, window=window,
+        l2="inputs (%.1f GB per GPU) are far larger than the 126 MB L2; no flush needed" % (N * bytes_per_point / 1e9))
+    del X, S
+    torch.cuda.empty_cache()
+    return res
+
+
+def run_b200(args, wl):
+    import torch
+    import torch.distributed as dist
+    from density_deconvolution_b200 import ops
+
+    env = Env()
+    env.world = world = int(os.environ.get("WORLD_SIZE", "1"))
+    env.rank = rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the B200 path has no CPU fallback; use --impl reference)")
+    torch.cuda.set_device(local_rank)
+    env.dev = dev = torch.device("cuda", local_rank)
+    env.ops, env.dist = ops, dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if world != args.gpus and rank == 0:
+        print("bench.py: WORLD_SIZE=%d but --gpus %d; using WORLD_SIZE" % (world, args.gpus), file=sys.stderr)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    env.barrier = barrier
+
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    env.hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    env.hbm_source = "MEASURED_PEAKS.json" if peaks else "fallback of B200_PROFILING.md"
 
     sampler = None
     if rank == 0:
@@ -278,93 +478,49 @@ def run_b200(args, wl):
         sampler = ClockSampler(gpu_id)
         sampler.start()
 
-    fp32_peak = ops.fp32_probe(dev)
-
-    # ---- the timed region: K EM iterations ------------------------------------------------
-    params = fresh()
-    for _ in range(max(args.warmup, 3)):
-        em_step(params)
-    ops.pair_timing(True)
-    t_em, window = timed(em_step, params, args.steps)
-    pair_ms = ops.pair_times()
-    ops.pair_timing(False)
-    ll_after = (stats[-4] + stats[-3]).item() / n_total
-    nonpd = stats[-1].item()
-
-    # ---- log-likelihood-only pass (score_batch), same protocol ------------------------------
-    for _ in range(3):
-        ll_step(params)
-    ops.pair_timing(True)
-    t_ll, _ = timed(ll_step, params, args.steps)
-    pair_ms_ll = ops.pair_times()
-    ops.pair_timing(False)
-
-    # ---- minibatch SGD steps through the estimator API (configs[4]: Adam, lr 1e-3, w 1e-3) --------
-    sgd = None
-    if not args.no_sgd:
-        sgd = run_sgd(args, wl, dev, world, X, S, fresh, barrier)
-
+    env.fp32_peak = ops.fp32_probe(dev)
+    steps, warmup = args.steps, max(args.warmup, 3)
+    N = args.points or wl["N"]
+    head = measure(env, args, args.workload, wl, N, steps, warmup, not args.no_sgd, not args.no_e2e)
+    window = head.pop("window")
     if sampler:
         time.sleep(0.06)
-        sampler.stop()
     clocks = sampler.summary(*window) if sampler else None
 
-    # ---- end to end through the host-buffer C ABI (pinned host memory -> GPU -> host) --------
-    e2e = None
-    if not args.no_e2e:
-        e2e = run_e2e(args, wl, ops, dist, dev, world, X, S, fresh, n_total, w_reg, barrier)
+    secondary = {}
+    names = [] if args.secondary in ("", "none") else [s for s in args.secondary.split(",") if s]
+    for key in names:
+        if key == args.workload or key not in WORKLOADS:
+            continue
+        w2 = dict(WORKLOADS[key])
+        r = measure(env, args, key, w2, w2["N"], max(2, min(steps, 5)), 3, not args.no_sgd, False)
+        win2 = r.pop("window")
+        r["clocks"] = sampler.summary(*win2) if sampler else None
+        secondary[key] = r
+    if sampler:
+        sampler.stop()
 
-    pairs_per_step = float(n_total) * K
-    value = pairs_per_step * args.steps / t_em
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-
-    pair_avg_s = (sum(pair_ms) / len(pair_ms)) * 1e-3 if pair_ms else None
-    pair_ll_avg_s = (sum(pair_ms_ll) / len(pair_ms_ll)) * 1e-3 if pair_ms_ll else None
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except OSError:
-        pass
-    hbm_peak = peaks.get("hbm_gbs", 6650.0)
-    bytes_per_point = 4 * (D + (D * D if wl["noise"] == "full" else D))
-    plan = ops.get_plan(1, D, K, N, noise=wl["noise"])
-    roofline = dict(
-        bound="fp32", kernel="pair_kernel<MODE_STATS>",
-        achieved=N * K * F_em(D) / pair_avg_s / 1e12, peak=fp32_peak / 1e12, unit="TFLOP/s",
-        frac=N * K * F_em(D) / pair_avg_s / fp32_peak,
-        peak_source="in-bench register-only FFMA probe on this GPU (MEASURED_PEAKS.json has no FP32 entry; "
-                    "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)",
-        flops_per_pair=F_em(D), pairs_per_launch=N * K, launch_ms=pair_avg_s * 1e3,
-        share_of_step=pair_avg_s * args.steps / t_em if world == 1 else None,
-        traffic=ncu_traffic(args.workload, "pair_kernel<MODE_STATS>") if not args.points else None,
-        traffic_note="DRAM bytes per launch from the committed ncu --set full capture (profiles/ncu_traffic.json); "
-                     "algorithmic bytes per launch = %d" % (N * bytes_per_point),
-        hbm=dict(achieved=N * bytes_per_point / pair_avg_s / 1e9, peak=hbm_peak, unit="GB/s",
-                 frac=N * bytes_per_point / pair_avg_s / 1e9 / hbm_peak,
-                 peak_source="MEASURED_PEAKS.json" if peaks else "fallback of B200_PROFILING.md"),
-        loglik_kernel=dict(kernel="pair_kernel<MODE_LOGLIK>", launch_ms=pair_ll_avg_s * 1e3,
-                           achieved=N * K * F_ll(D) / pair_ll_avg_s / 1e12,
-                           frac=N * K * F_ll(D) / pair_ll_avg_s / fp32_peak, flops_per_pair=F_ll(D)))
+    D, K = wl["D"], wl["K"]
     line = dict(
-        metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
-        ms_per_step=t_em / args.steps * 1e3, higher_is_better=True, scaling="weak", vs_baseline=None,
-        dtype="f32", data="synthetic",
-        config=dict(workload=wl["name"], points_per_gpu=N, points_total=n_total, D=D, K=K, noise=wl["noise"],
+        metric=METRIC, value=head["value"], unit=UNIT, n_gpus=world, steps=steps, warmup=warmup,
+        ms_per_step=head["ms_per_step"], higher_is_better=True, scaling="weak", vs_baseline=None,
+        dtype="f32", data=head["data"] if head["data"] == "synthetic" else "real table tiled, synthetic noise",
+        config=dict(workload=head["workload"], points_per_gpu=head["points_per_gpu"], points_total=head["points_total"],
+                    D=D, K=K, noise=wl["noise"],
                     step="one EM iteration: fused log-lik + E-step + M-step statistics kernel, "
                          "stats all-reduce (N>1), closed-form parameter update",
-                    l2="inputs (%.1f GB per GPU) are far larger than the 126 MB L2; no flush needed"
-                       % (N * bytes_per_point / 1e9),
-                    parallelism="points sharded by rank, %d rank(s)" % world, launch_plan=plan),
-        em_iters_per_sec=args.steps / t_em,
-        loglik_only=dict(value=pairs_per_step * args.steps / t_ll, unit=UNIT, ms_per_pass=t_ll / args.steps * 1e3),
-        mean_loglik_after=ll_after, nonpd_pairs=nonpd,
-        gpu_launches=4 * args.steps,
-        gpu_launches_note="per step: prepare_kernel, pair_kernel<STATS>, finalize_stats_kernel, mstep_kernel",
-        sgd=sgd, clocks=clocks, roofline=roofline, e2e=e2e)
+                    l2=head["l2"], parallelism="points sharded by rank, %d rank(s)" % world,
+                    launch_plan=head["launch_plan"]),
+        em_iters_per_sec=head["em_iters_per_sec"], loglik_only=head["loglik_only"],
+        mean_loglik_after=head["mean_loglik_after"], nonpd_pairs=head["nonpd_pairs"],
+        gpu_launches=head["gpu_launches"], gpu_launches_note=head["gpu_launches_note"],
+        sgd=head["sgd"], sgd_ms_per_step=head["sgd"]["ms_per_step"] if head["sgd"] else None,
+        sgd_roofline_frac=head["sgd"]["roofline_frac"] if head["sgd"] else None,
+        clocks=clocks, roofline=head["roofline"], e2e=head["e2e"], secondary=secondary)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(wl)
     emit(line)
@@ -372,12 +528,13 @@ def run_b200(args, wl):
         dist.destroy_process_group()
 
 
-def run_sgd(args, wl, dev, world, X, S, fresh, barrier, n_steps=20):
+def run_sgd(args, env, wl, X, S, fresh, n_steps=20):
     """Minibatch-SGD steps (forward + backward in ONE fused statistics launch, stats all-reduce,
     Adam on the [K,.] parameters) through ``SGDDeconvGMM.fit`` on a resident slice of the shard:
     ``n_steps`` minibatches of ``--sgd-batch`` points per GPU, one epoch, device-side shuffling."""
     import torch
     from density_deconvolution_b200.estimators import SGDDeconvGMM
+    dev, world = env.dev, env.world
     N, D = X.shape
     K = wl["K"]
     B = min(args.sgd_batch, N)
@@ -398,17 +555,16 @@ def run_sgd(args, wl, dev, world, X, S, fresh, barrier, n_steps=20):
 
     make().fit((X[:min(3 * B, n_sub)], S[:min(3 * B, n_sub)]), init=False)       # warm-up (3 steps)
     est = make()
-    barrier()
+    env.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     est.fit((X[:n_sub], S[:n_sub]), init=False)
     e1.record()
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    barrier()
+    env.barrier()
     if world > 1:
-        import torch.distributed as dist
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        env.dist.all_reduce(ms, op=env.dist.ReduceOp.MAX)
     t = ms.item() * 1e-3
     return dict(api="SGDDeconvGMM.fit (1 epoch, device-resident batches, shuffle on device)",
                 batch_per_gpu=B, global_batch=B * world, steps=n_steps, ms_per_step=t / n_steps * 1e3,
@@ -416,17 +572,36 @@ def run_sgd(args, wl, dev, world, X, S, fresh, barrier, n_steps=20):
                 pair_evals_per_sec=float(n_sub) * world * K / t, mean_loglik=est.train_loss_curve[-1])
 
 
-def run_e2e(args, wl, ops, dist, dev, world, X, S, fresh, n_total, w_reg, barrier):
+def host_mem_available():
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) * 1024
+    except OSError:
+        pass
+    return None
+
+
+def run_e2e(args, env, wl, X, S, fresh, n_total, w_reg, steps):
     """The same EM iteration through the host-buffer C ABI: every step streams the rank's shard
     from pinned host memory (H2D inside the timed region) and reads the updated parameters and
-    the log-likelihood back (D2H)."""
+    the log-likelihood back (D2H).  The pinned copy of the shard is bounded by the host memory that is
+    free (a third of MemAvailable shared by the ranks): a prefix of the shard is streamed when it does not fit."""
     import torch
+    ops, dist, dev, world = env.ops, env.dist, env.dev, env.world
     N, D = X.shape
     K = wl["K"]
-    hX = torch.empty(X.shape, dtype=torch.float32, pin_memory=True)
-    hS = torch.empty(S.shape, dtype=torch.float32, pin_memory=True)
-    hX.copy_(X)
-    hS.copy_(S)
+    bytes_per_point = 4 * (D + S[0].numel())
+    avail = host_mem_available()
+    n_e2e = N
+    if avail is not None:
+        n_e2e = int(min(N, max(1 << 18, (avail // 3) // max(world, 1) // bytes_per_point)))
+    n_e2e_total = n_e2e * world
+    hX = torch.empty((n_e2e, D), dtype=torch.float32, pin_memory=True)
+    hS = torch.empty((n_e2e,) + tuple(S.shape[1:]), dtype=torch.float32, pin_memory=True)
+    hX.copy_(X[:n_e2e])
+    hS.copy_(S[:n_e2e])
     a, _, m, Sg = fresh()
     ha, hm, hSg = a.cpu(), m.cpu(), Sg.cpu()
     ctx = ops.HostContext(D, K, chunk_points=1 << 18, device=dev.index)
@@ -442,29 +617,31 @@ def run_e2e(args, wl, ops, dist, dev, world, X, S, fresh, n_total, w_reg, barrie
         dist.all_reduce(d_stats)
         d_par[2].copy_(hm)
         d_par[3].copy_(hSg)
-        ops.mstep_update(d_stats, n_total, w_reg, d_par[2], d_par[3], d_par[0], d_par[1])
+        ops.mstep_update(d_stats, n_e2e_total, w_reg, d_par[2], d_par[3], d_par[0], d_par[1])
         ha.copy_(d_par[0])
         hm.copy_(d_par[2])
         hSg.copy_(d_par[3])
         return float(d_stats[-4].item() + d_stats[-3].item())
 
-    steps = max(2, min(args.steps, 5))
+    nsteps = max(2, min(steps, 5))
     step()
-    barrier()
+    env.barrier()
     t0 = time.perf_counter()
-    for _ in range(steps):
+    for _ in range(nsteps):
         ll = step()
     torch.cuda.synchronize()
     dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    barrier()
+    env.barrier()
     if world > 1:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
     ctx.close()
     bytes_in = 4 * (hX.numel() + hS.numel() + K * (1 + D + D * D))
     bytes_out = 4 * (K * (1 + D + D * D)) + 16
-    return dict(value=float(n_total) * K * steps / dt.item(), unit=UNIT, steps=steps,
-                ms_per_step=dt.item() / steps * 1e3, em_iters_per_sec=steps / dt.item(),
-                h2d_bytes_per_step=bytes_in, d2h_bytes_per_step=bytes_out, mean_loglik=ll / n_total,
+    del hX, hS
+    return dict(value=float(n_e2e_total) * K * nsteps / dt.item(), unit=UNIT, steps=nsteps,
+                ms_per_step=dt.item() / nsteps * 1e3, em_iters_per_sec_on_streamed_points=nsteps / dt.item(),
+                points_per_gpu_streamed=n_e2e, whole_shard=(n_e2e == N),
+                h2d_bytes_per_step=bytes_in, d2h_bytes_per_step=bytes_out, mean_loglik=ll / n_e2e_total,
                 api="dgmm_em_iteration_host (N=1) / dgmm_estep_stats_host + all-reduce + dgmm_mstep_update_f32 (N>1), "
                     "pinned host buffers, 262144-point chunks, copy/compute overlap on two streams")
 

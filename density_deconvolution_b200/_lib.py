@@ -18,11 +18,12 @@ MAX_D, MAX_K = 32, 256
 _ERRORS = {
     -1: "bad argument", -2: "unsupported dimension D (1..32)", -3: "unsupported component count K (1..256)",
     -4: "workspace too small", -5: "unknown noise layout", -6: "no sm_100 CUDA device",
+    -7: "out_ll is required for this shape (dgmm_stats_needs_ll)",
 }
 
 # every symbol include/dgmm_b200.h declares (tests check the list against the header)
 SYMBOLS = (
-    "dgmm_abi_version", "dgmm_supported_dims", "dgmm_workspace_bytes", "dgmm_loglik_f32",
+    "dgmm_abi_version", "dgmm_supported_dims", "dgmm_workspace_bytes", "dgmm_stats_needs_ll", "dgmm_loglik_f32",
     "dgmm_estep_stats_f32", "dgmm_estep_full_f32", "dgmm_mstep_update_f32", "dgmm_online_mstep_f32",
     "dgmm_fp32_probe",
     "dgmm_ctx_create", "dgmm_ctx_destroy", "dgmm_em_iteration_host", "dgmm_estep_stats_host", "dgmm_score_host",
@@ -70,6 +71,8 @@ def lib():
     L.dgmm_supported_dims.argtypes = [ctypes.POINTER(i32), ctypes.POINTER(i32)]
     L.dgmm_workspace_bytes.restype = sz
     L.dgmm_workspace_bytes.argtypes = [i32, i32]
+    L.dgmm_stats_needs_ll.restype = i32
+    L.dgmm_stats_needs_ll.argtypes = [i32, i32, i32]
     L.dgmm_loglik_f32.restype = i32
     L.dgmm_loglik_f32.argtypes = [vp, vp, i32, i64, i32, i32, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     L.dgmm_estep_stats_f32.restype = i32

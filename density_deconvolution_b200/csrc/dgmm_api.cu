@@ -13,6 +13,7 @@
 
 #include "../../include/dgmm_b200.h"
 #include "dgmm_tables.cuh"
+#include "dgmm_team_geo.cuh"
 
 // per-D lookup functions, one translation unit each (dgmm_inst_dXX.cu)
 #define DGMM_DECL(D)                                                          \
@@ -25,6 +26,11 @@ DGMM_DECL(9) DGMM_DECL(10) DGMM_DECL(11) DGMM_DECL(12) DGMM_DECL(13) DGMM_DECL(1
 DGMM_DECL(17) DGMM_DECL(18) DGMM_DECL(19) DGMM_DECL(20) DGMM_DECL(21) DGMM_DECL(22) DGMM_DECL(23) DGMM_DECL(24)
 DGMM_DECL(25) DGMM_DECL(26) DGMM_DECL(27) DGMM_DECL(28) DGMM_DECL(29) DGMM_DECL(30) DGMM_DECL(31) DGMM_DECL(32)
 #undef DGMM_DECL
+// cooperative (team) kernels, D = 17..32 (dgmm_team_dXX.cu)
+#define DGMM_TDECL(D) dgmm::TeamKernels dgmm_team_lookup_d##D();
+DGMM_TDECL(17) DGMM_TDECL(18) DGMM_TDECL(19) DGMM_TDECL(20) DGMM_TDECL(21) DGMM_TDECL(22) DGMM_TDECL(23) DGMM_TDECL(24)
+DGMM_TDECL(25) DGMM_TDECL(26) DGMM_TDECL(27) DGMM_TDECL(28) DGMM_TDECL(29) DGMM_TDECL(30) DGMM_TDECL(31) DGMM_TDECL(32)
+#undef DGMM_TDECL
 
 namespace {
 
@@ -46,6 +52,15 @@ const DimRow kDims[DGMM_MAX_D + 1] = {
     DGMM_ROW(9),  DGMM_ROW(10), DGMM_ROW(11), DGMM_ROW(12), DGMM_ROW(13), DGMM_ROW(14), DGMM_ROW(15), DGMM_ROW(16),
     DGMM_ROW(17), DGMM_ROW(18), DGMM_ROW(19), DGMM_ROW(20), DGMM_ROW(21), DGMM_ROW(22), DGMM_ROW(23), DGMM_ROW(24),
     DGMM_ROW(25), DGMM_ROW(26), DGMM_ROW(27), DGMM_ROW(28), DGMM_ROW(29), DGMM_ROW(30), DGMM_ROW(31), DGMM_ROW(32)};
+
+typedef TeamKernels (*team_lookup_t)();
+const team_lookup_t kTeam[DGMM_MAX_D + 1] = {
+    nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+    nullptr, nullptr, nullptr, nullptr,
+    dgmm_team_lookup_d17, dgmm_team_lookup_d18, dgmm_team_lookup_d19, dgmm_team_lookup_d20, dgmm_team_lookup_d21,
+    dgmm_team_lookup_d22, dgmm_team_lookup_d23, dgmm_team_lookup_d24, dgmm_team_lookup_d25, dgmm_team_lookup_d26,
+    dgmm_team_lookup_d27, dgmm_team_lookup_d28, dgmm_team_lookup_d29, dgmm_team_lookup_d30, dgmm_team_lookup_d31,
+    dgmm_team_lookup_d32};
 
 #define CUDA_TRY(x)                                  \
     do {                                             \
@@ -106,6 +121,10 @@ struct Workspace {
     int* nonpd;
     double* part_ll;
     float* part;
+    // cooperative path (D > 16): parameters in the register order of the team lanes
+    float* team_sig;
+    float* team_mu;
+    float* team_cj;
     size_t bytes;
 };
 
@@ -119,8 +138,16 @@ Workspace carve(void* base, int D, int K, int sms) {
     w.cj = (float*)(b + off);       off += up256((size_t)GS * 4);
     w.nonpd = (int*)(b + off);      off += 256;
     const int mg = max_grid(D, K, sms);
-    w.part_ll = (double*)(b + off); off += up256((size_t)mg * 2 * 8);
+    // (the cooperative path keeps the partial sums of its two passes side by side)
+    w.part_ll = (double*)(b + off); off += up256((size_t)mg * (D > 16 ? 4 : 2) * 8);
     w.part = (float*)(b + off);     off += up256((size_t)mg * ns_of(D) * kPairMaxThreads * 4);
+    w.team_sig = w.team_mu = w.team_cj = nullptr;
+    if (D > 16) {
+        const size_t Kp = (size_t)K + team::kMaxTB;
+        w.team_sig = (float*)(b + off); off += up256(Kp * team::geo_nreg(D) * team::kP * 4);
+        w.team_mu = (float*)(b + off);  off += up256(Kp * team::geo_R(D) * team::kP * 4);
+        w.team_cj = (float*)(b + off);  off += up256(Kp * 4);
+    }
     w.bytes = off;
     return w;
 }
@@ -472,7 +499,7 @@ int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int no
     p.gcls = group_class(p.GS);
     const Tuning& t = g_tuning;
     const bool force_fallback = (t.sigp == ST_GLOBAL && t.accp == ST_GLOBAL);
-    int which = (t.rc > 0) ? t.rc : 0;
+    int which = (t.rc == 1 || t.rc == 2) ? t.rc : 0;   // rc = 3 / 4 choose between the kernel families (use_team_path)
     PairVariant v{nullptr, 0, 0, 0, 0, 0, 0};
     const int nz = (noise == NOISE_FULL) ? NZ_FULL : NZ_DIAG;
     bool ok = false;
@@ -485,7 +512,7 @@ int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int no
             ok = v.fn && fit_geometry(dev, v, mode, D, noise, has_g, &p);
         }
     }
-    if (ok && which == 0 && D > 16 && v.sigp == ST_SMEM && t.rc < 0 && 2 * (p.smem + 1024) > (size_t)dev.smem_optin) {
+    if (ok && which == 0 && D > 16 && v.sigp == ST_SMEM && (t.rc < 0 || t.rc == 4) && 2 * (p.smem + 1024) > (size_t)dev.smem_optin) {
         // D = 17..24: Sigma_j columns in shared memory leave room for one block per SM only
         Plan q = p;
         const PairVariant alt = kDims[D].pair(mode, 1, p.gcls, nz);
@@ -581,6 +608,250 @@ void timing_end(int slot, cudaStream_t st) {
     ++g_timing.count;
 }
 
+// ---------------------------------------------------------------------------------------
+// cooperative (team) path, D > 16: parameter layout, launch plan, finalise
+// ---------------------------------------------------------------------------------------
+
+// Mixture parameters in the register order of the team lanes (dgmm_team.cuh):
+//   team_sig[((j * NQ + q) * 8 + l) * 4 + c] = lower(Sigma_j + S_shared)[a][b],  4q + c -> (slot r, column b), a = l + 8r
+// (0 outside the lower triangle / beyond D; identity for the padding components j >= K),
+//   team_mu[(j * R + r) * 8 + l] = mu_j[a],  team_cj[j] = log alpha_j - D/2 log 2pi (-inf for j >= K).
+__global__ void team_prepare_kernel(const float* __restrict__ log_alpha, const float* __restrict__ mu,
+                                    const float* __restrict__ Sigma, const float* __restrict__ S_shared, int D, int K,
+                                    int Kp, team::GeoRT geo, float* __restrict__ sig, float* __restrict__ muT,
+                                    float* __restrict__ cj, int* __restrict__ nonpd) {
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nth = (long long)gridDim.x * blockDim.x;
+    if (tid == 0 && nonpd) *nonpd = 0;
+    const int per = geo.NREG * team::kP;
+    for (long long idx = tid; idx < (long long)Kp * per; idx += nth) {
+        const int j = (int)(idx / per), rem = (int)(idx - (long long)j * per);
+        const int q = rem / 32, l = (rem % 32) / 4, c = rem % 4;
+        const int flat = 4 * q + c;
+        int r = 0;
+        while (r + 1 < geo.R && flat >= geo.off[r + 1]) ++r;
+        const int b = flat - geo.off[r], a = l + 8 * r;
+        float v = 0.f;
+        if (a < D && b <= a) {
+            if (j < K) {
+                v = Sigma[((size_t)j * D + a) * D + b];
+                if (S_shared) v += S_shared[a * D + b];
+            } else {
+                v = (a == b) ? 1.f : 0.f;
+            }
+        }
+        sig[idx] = v;
+    }
+    for (long long idx = tid; idx < (long long)Kp * geo.R * team::kP; idx += nth) {
+        const int j = (int)(idx / (geo.R * team::kP)), rem = (int)(idx % (geo.R * team::kP));
+        const int r = rem / team::kP, l = rem % team::kP, a = l + 8 * r;
+        muT[idx] = (j < K && a < D) ? mu[(size_t)j * D + a] : 0.f;
+    }
+    for (long long j = tid; j < Kp; j += nth) cj[j] = (j < K) ? (log_alpha[j] - D * kHalfLog2Pi) : -INFINITY;
+}
+
+// Sums the per-block partials of the team statistics pass ([grid][TB][NS], block = slice * n_chunks + chunk)
+// over the slices in a fixed order (double accumulation: deterministic) into the packed buffer; the last
+// block assembles the tail from the two passes' (sum ll | sum g) partials.
+__global__ void __launch_bounds__(128) team_finalize_kernel(const float* __restrict__ part, const double* __restrict__ pll1,
+                                                            int grid1, const double* __restrict__ pll2, int grid2,
+                                                            const int* __restrict__ nonpd, int D, int K, int TB,
+                                                            int n_chunks, int n_slices, float* __restrict__ stats,
+                                                            int beta) {
+    const int ND = D * (D + 1) / 2, NS = 1 + D + ND;
+    const int total = K * (1 + D + D * D);
+    const int j = blockIdx.x;
+    if (j < K) {
+        const int chunk = j / TB, tm = j - chunk * TB;
+        for (int e = threadIdx.x; e < NS; e += blockDim.x) {
+            double s = 0.0;
+            for (int sl = 0; sl < n_slices; ++sl)
+                s += (double)part[(((size_t)sl * n_chunks + chunk) * TB + tm) * NS + e];
+            const float v = (float)s;
+            if (e == 0) {
+                stats[j] = beta ? stats[j] + v : v;
+            } else if (e < 1 + D) {
+                float* o = stats + K + j * D + (e - 1);
+                *o = beta ? *o + v : v;
+            } else {
+                int a = 0;
+                const int tt = e - 1 - D;
+                while ((a + 1) * (a + 2) / 2 <= tt) ++a;
+                const int b = tt - a * (a + 1) / 2;
+                float* base = stats + K + K * D + (size_t)j * D * D;
+                const float nv = beta ? base[a * D + b] + v : v;
+                base[a * D + b] = nv;
+                base[b * D + a] = nv;
+            }
+        }
+    } else {
+        __shared__ double sh[2][128];
+        double ll = 0.0, sg = 0.0;
+        for (int b = threadIdx.x; b < grid1; b += blockDim.x) ll += pll1[2 * b];
+        for (int b = threadIdx.x; b < grid2; b += blockDim.x) sg += pll2[2 * b];
+        sh[0][threadIdx.x] = ll;
+        sh[1][threadIdx.x] = sg;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            ll = 0.0; sg = 0.0;
+            for (int x = 0; x < (int)blockDim.x; ++x) { ll += sh[0][x]; sg += sh[1][x]; }
+            float* tail = stats + total;
+            if (beta) ll += (double)tail[0] + (double)tail[1];
+            const float hi = (float)ll;
+            tail[0] = hi;
+            tail[1] = isfinite(hi) ? (float)(ll - (double)hi) : 0.f;
+            tail[2] = beta ? tail[2] + (float)sg : (float)sg;
+            tail[3] = beta ? tail[3] + (float)(*nonpd) : (float)(*nonpd);
+        }
+    }
+}
+
+struct TeamPlan {
+    const void* kernel = nullptr;
+    int TB, TPB, n_chunks, n_slices, grid, PT, NST, use_bulk, tmem_cols, nz;
+    size_t smem;
+    long long n_tiles;
+};
+
+// Which path serves (D, K): the cooperative kernels for D >= 21 and wherever the thread-per-pair family
+// has no unrolled variant (K < 64 above D = 16); tuning rc = 3 forces the team path, rc = 4 the pair path.
+bool use_team_path(int D, int K, int mode, int noise) {
+    if (D <= 16) return false;
+    if (g_tuning.rc == 3) return true;
+    const int nz = (noise == NOISE_FULL) ? NZ_FULL : NZ_DIAG;
+    const PairVariant v = kDims[D].pair(mode, 0, group_class(group_size(K)), nz);
+    if (!v.fn) return true;
+    if (g_tuning.rc == 4) return false;
+    return D >= 21;
+}
+
+int make_team_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int noise, bool has_g, const void* X,
+                   const void* S, const void* g, const void* ll, TeamPlan* out) {
+    TeamPlan p;
+    const Tuning& t = g_tuning;
+    p.n_chunks = (K + team::kMaxTB - 1) / team::kMaxTB;
+    p.TB = (((K + p.n_chunks - 1) / p.n_chunks) + 3) & ~3;
+    p.TPB = p.TB * team::kP;
+    p.PT = t.pt > 0 ? ((t.pt + 3) & ~3) : 4;
+    p.NST = t.nst > 0 ? std::min(t.nst, kMaxStages) : 2;
+    const bool stats = (mode == MODE_STATS);
+    p.nz = (noise == NOISE_FULL || noise == NOISE_DIAG) ? team::TNZ_MATRIX : team::TNZ_NONE;
+    const TeamKernels tk = kTeam[D]();
+    p.kernel = stats ? tk.stats[p.nz] : tk.loglik[p.nz];
+    if (!p.kernel) return DGMM_ERR_UNSUPPORTED_D;
+    for (;;) {
+        p.smem = team::team_smem_bytes(D, noise, p.PT, p.NST, has_g, stats, p.TPB);
+        if (p.smem <= (size_t)dev.smem_optin) break;
+        if (p.NST > 1) { --p.NST; continue; }
+        return DGMM_ERR_UNSUPPORTED_K;
+    }
+    CUDA_TRY(cudaFuncSetAttribute(p.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+    int occ = 0;
+    p.tmem_cols = 0;
+    cudaFuncAttributes fa;
+    CUDA_TRY(cudaFuncGetAttributes(&fa, p.kernel));
+    int smem_sm = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev.device));
+    {
+        // residency from registers, shared memory, threads and (statistics pass) the 512 tensor-memory columns;
+        // the occupancy query answers 1 block/SM for any kernel that allocates tensor memory
+        const int regs_per_block = ((fa.numRegs + 7) & ~7) * p.TPB;
+        int o = 65536 / std::max(regs_per_block, 1);
+        o = std::min<int>(o, smem_sm / (int)(p.smem + fa.sharedSizeBytes + 1024));
+        o = std::min(o, 2048 / p.TPB);
+        o = std::min(o, 32);
+        if (stats) {
+            p.tmem_cols = tmem_alloc_cols(team::geo_nacc(D), p.TPB / 32);
+            if (p.tmem_cols > 512) return DGMM_ERR_UNSUPPORTED_D;
+            o = std::min(o, 512 / p.tmem_cols);
+        }
+        occ = std::max(o, 1);
+    }
+    if (t.blocks_per_sm > 0) occ = std::min(occ, t.blocks_per_sm);
+    p.n_tiles = (N + p.PT - 1) / p.PT;
+    const long long cap = std::min<long long>((long long)dev.sms * occ, max_grid(D, K, dev.sms));
+    if (stats) {
+        long long sl = std::max<long long>(1, cap / p.n_chunks);
+        sl = std::min<long long>(sl, std::max<long long>(p.n_tiles, 1));
+        p.n_slices = (int)sl;
+        p.grid = p.n_slices * p.n_chunks;
+    } else {
+        p.n_slices = 0;
+        p.grid = (int)std::min<long long>(cap, std::max<long long>(p.n_tiles, 1));
+    }
+    const bool aligned = (((uintptr_t)X | (uintptr_t)(noise == NOISE_FULL || noise == NOISE_DIAG ? S : nullptr) |
+                           (uintptr_t)g | (uintptr_t)ll) & 15) == 0;
+    p.use_bulk = (aligned && !t.no_bulk) ? 1 : 0;
+    *out = p;
+    return 0;
+}
+
+// Cooperative path of run_pair: prepare + log-likelihood pass (+ statistics pass).  `ll` [N] is required
+// (it carries ll_i from the first pass to the second).  MODE_STATS leaves the partial sums of both passes in
+// the workspace: call launch_team_finalize afterwards.
+struct TeamRun {
+    TeamPlan ll_plan, st_plan;
+};
+int run_team(int mode, const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+             const float* mu, const float* Sigma, const float* g, float resp_floor, float* ll, const DeviceInfo& dev,
+             const Workspace& ws, cudaStream_t st, TeamRun* run) {
+    if (!ll) return DGMM_ERR_BAD_ARG;
+    const team::GeoRT geo = team::geo_rt(D);
+    int rc = make_team_plan(dev, MODE_LOGLIK, D, K, N, noise, false, X, S, nullptr, ll, &run->ll_plan);
+    if (rc) return rc;
+    if (mode == MODE_STATS) {
+        rc = make_team_plan(dev, MODE_STATS, D, K, N, noise, g != nullptr, X, S, g, ll, &run->st_plan);
+        if (rc) return rc;
+    }
+    const TeamPlan& lp = run->ll_plan;
+    const int Kp = lp.n_chunks * lp.TB;
+    team_prepare_kernel<<<64, 256, 0, st>>>(log_alpha, mu, Sigma, noise == NOISE_SHARED ? S : nullptr, D, K, Kp, geo,
+                                            ws.team_sig, ws.team_mu, ws.team_cj, ws.nonpd);
+    CUDA_TRY(cudaGetLastError());
+
+    auto fill = [&](const TeamPlan& pl, bool stats, bool has_g) {
+        team::TeamParams p;
+        p.X = X; p.S = S; p.g = stats ? g : nullptr;
+        p.sigT = ws.team_sig; p.muT = ws.team_mu; p.cj = ws.team_cj;
+        p.ll = ll; p.out_ll = nullptr;
+        p.part = ws.part;
+        p.part_ll = stats ? ws.part_ll + 2 * (size_t)max_grid(D, K, dev.sms) : ws.part_ll;
+        p.nonpd = ws.nonpd;
+        p.N = N; p.n_tiles = pl.n_tiles;
+        p.K = K; p.TB = pl.TB; p.n_chunks = pl.n_chunks; p.n_slices = pl.n_slices; p.PT = pl.PT; p.NST = pl.NST;
+        p.noise = noise; p.use_bulk = pl.use_bulk;
+        p.resp_floor = resp_floor;
+        const team::TeamStage SL = team::team_stage(D, noise, pl.PT, has_g, stats);
+        p.n_s = noise_floats_per_point(D, noise);
+        p.off_X = SL.off_X; p.off_g = SL.off_g; p.off_ll = SL.off_ll; p.stage_bytes = SL.bytes;
+        p.tmem_cols = pl.tmem_cols;
+        return p;
+    };
+    const int tslot = timing_begin(st);
+    {
+        team::TeamParams p = fill(lp, false, false);
+        void* args[] = {&p};
+        CUDA_TRY(cudaLaunchKernel(lp.kernel, dim3(lp.grid), dim3(lp.TPB), args, lp.smem, st));
+    }
+    if (mode == MODE_STATS) {
+        const TeamPlan& sp = run->st_plan;
+        team::TeamParams p = fill(sp, true, g != nullptr);
+        void* args[] = {&p};
+        CUDA_TRY(cudaLaunchKernel(sp.kernel, dim3(sp.grid), dim3(sp.TPB), args, sp.smem, st));
+    }
+    timing_end(tslot, st);
+    return 0;
+}
+
+int launch_team_finalize(const TeamRun& run, const DeviceInfo& dev, const Workspace& ws, int D, int K, float* out_stats,
+                         int beta, cudaStream_t st) {
+    const TeamPlan& sp = run.st_plan;
+    team_finalize_kernel<<<K + 1, 128, 0, st>>>(ws.part, ws.part_ll, run.ll_plan.grid,
+                                                ws.part_ll + 2 * (size_t)max_grid(D, K, dev.sms), sp.grid, ws.nonpd, D, K,
+                                                sp.TB, sp.n_chunks, sp.n_slices, out_stats, beta);
+    return (int)cudaGetLastError();
+}
+
 // Runs prepare + pair kernel; leaves partials in the workspace.  Returns the plan.
 int run_pair(int mode, const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
              const float* mu, const float* Sigma, const float* g, float resp_floor, float* out_ll, void* workspace,
@@ -624,6 +895,62 @@ int run_pair(int mode, const float* X, const float* S, int noise, int64_t N, int
     return 0;
 }
 
+// Log-likelihood pass on whichever kernel family serves (D, K); *nblk = per-block (sum ll) partials written.
+int loglik_pass(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+                const float* mu, const float* Sigma, float* out_ll, void* workspace, size_t workspace_bytes,
+                cudaStream_t st, Workspace* ws_out, int* nblk) {
+    if (use_team_path(D, K, MODE_LOGLIK, noise)) {
+        DeviceInfo dev;
+        int rc = device_info(&dev);
+        if (rc) return rc;
+        if (!workspace) return DGMM_ERR_WORKSPACE;
+        const Workspace ws = carve(workspace, D, K, dev.sms);
+        if (ws.bytes > workspace_bytes) return DGMM_ERR_WORKSPACE;
+        TeamRun run;
+        rc = run_team(MODE_LOGLIK, X, S, noise, N, D, K, log_alpha, mu, Sigma, nullptr, 0.f, out_ll, dev, ws, st, &run);
+        if (rc) return rc;
+        *ws_out = ws;
+        *nblk = run.ll_plan.grid;
+        return 0;
+    }
+    Plan plan;
+    int rc = run_pair(MODE_LOGLIK, X, S, noise, N, D, K, log_alpha, mu, Sigma, nullptr, 0.f, out_ll, workspace,
+                      workspace_bytes, st, &plan, ws_out);
+    if (rc) return rc;
+    *nblk = plan.grid;
+    return 0;
+}
+
+// Fused statistics pass + finalise into out_stats (beta = 1 accumulates) on whichever family serves (D, K).
+// The cooperative path needs ll_scratch [N] (it may be the caller's out_ll).
+int stats_pass(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+               const float* mu, const float* Sigma, const float* g, float resp_floor, float* out_ll, float* out_stats,
+               int beta, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+    if (use_team_path(D, K, MODE_STATS, noise)) {
+        if (!out_ll) return DGMM_ERR_LL_REQUIRED;
+        DeviceInfo dev;
+        int rc = device_info(&dev);
+        if (rc) return rc;
+        if (!workspace) return DGMM_ERR_WORKSPACE;
+        const Workspace ws = carve(workspace, D, K, dev.sms);
+        if (ws.bytes > workspace_bytes) return DGMM_ERR_WORKSPACE;
+        TeamRun run;
+        rc = run_team(MODE_STATS, X, S, noise, N, D, K, log_alpha, mu, Sigma, g, resp_floor, out_ll, dev, ws, st, &run);
+        if (rc) return rc;
+        return launch_team_finalize(run, dev, ws, D, K, out_stats, beta, st);
+    }
+    Plan plan;
+    Workspace ws;
+    int rc = run_pair(MODE_STATS, X, S, noise, N, D, K, log_alpha, mu, Sigma, g, resp_floor, out_ll, workspace,
+                      workspace_bytes, st, &plan, &ws);
+    if (rc) return rc;
+    const bool cols = (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM);
+    finalize_stats_kernel<<<ns_of(D) * ((K + 31) / 32) + 1, dim3(32, kFinY), 0, st>>>(
+        ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K, plan.GS, cols ? plan.TPB : plan.GS, cols ? plan.NSLOT : 1,
+        out_stats, beta);
+    return (int)cudaGetLastError();
+}
+
 }  // namespace
 
 // =======================================================================================
@@ -646,6 +973,11 @@ size_t dgmm_workspace_bytes(int D, int K) {
     DeviceInfo dev;
     if (device_info(&dev)) return 0;
     return carve(nullptr, D, K, dev.sms).bytes;
+}
+
+int dgmm_stats_needs_ll(int D, int K, int noise_layout) {
+    if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return 0;
+    return use_team_path(D, K, MODE_STATS, noise_layout) ? 1 : 0;
 }
 
 // Diagnostics / tuning hook (not part of the drop-in surface): -1 = automatic.
@@ -682,6 +1014,16 @@ int dgmm_debug_get_plan(int mode, int D, int K, int64_t N, int noise, int has_g,
     DeviceInfo dev;
     int rc = device_info(&dev);
     if (rc) return rc;
+    if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return DGMM_ERR_BAD_ARG;
+    if (use_team_path(D, K, mode, noise)) {
+        // cooperative path: sigp = 3 marks it; GS = teams per block, NSLOT = component chunks
+        TeamPlan t;
+        rc = make_team_plan(dev, mode, D, K, N, noise, has_g != 0, nullptr, nullptr, nullptr, nullptr, &t);
+        if (rc) return rc;
+        out[0] = 3; out[1] = ST_TMEM; out[2] = 3; out[3] = t.TB; out[4] = t.n_chunks; out[5] = t.TPB;
+        out[6] = t.PT; out[7] = t.NST; out[8] = t.grid; out[9] = (int)t.smem; out[10] = t.use_bulk;
+        return 0;
+    }
     Plan p;
     rc = make_plan(dev, mode, D, K, N, noise, has_g != 0, nullptr, nullptr, nullptr, &p);
     if (rc) return rc;
@@ -695,14 +1037,14 @@ int dgmm_loglik_f32(const float* X, const float* S, int noise_layout, int64_t N,
                     int* status, void* workspace, size_t workspace_bytes, void* stream) {
     int rc = check_common(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma);
     if (rc) return rc;
+    if (!out_ll) return DGMM_ERR_BAD_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    Plan plan;
     Workspace ws;
-    rc = run_pair(MODE_LOGLIK, X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, nullptr, 0.f, out_ll, workspace,
-                  workspace_bytes, st, &plan, &ws);
+    int nblk = 0;
+    rc = loglik_pass(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, out_ll, workspace, workspace_bytes, st, &ws, &nblk);
     if (rc) return rc;
     if (out_sum || status) {
-        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, plan.grid, out_sum, status, 0);
+        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, nblk, out_sum, status, 0);
         CUDA_TRY(cudaGetLastError());
     }
     return 0;
@@ -715,17 +1057,8 @@ int dgmm_estep_stats_f32(const float* X, const float* S, int noise_layout, int64
     int rc = check_common(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma);
     if (rc) return rc;
     if (!out_stats) return DGMM_ERR_BAD_ARG;
-    cudaStream_t st = (cudaStream_t)stream;
-    Plan plan;
-    Workspace ws;
-    rc = run_pair(MODE_STATS, X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, g, resp_floor, out_ll, workspace,
-                  workspace_bytes, st, &plan, &ws);
-    if (rc) return rc;
-    finalize_stats_kernel<<<ns_of(D) * ((K + 31) / 32) + 1, dim3(32, kFinY), 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
-                                                               plan.GS, (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.TPB : plan.GS,
-                                                               (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.NSLOT : 1, out_stats, 0);
-    CUDA_TRY(cudaGetLastError());
-    return 0;
+    return stats_pass(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, g, resp_floor, out_ll, out_stats, 0, workspace,
+                      workspace_bytes, (cudaStream_t)stream);
 }
 
 int dgmm_estep_full_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
@@ -736,10 +1069,9 @@ int dgmm_estep_full_f32(const float* X, const float* S, int noise_layout, int64_
     if (rc) return rc;
     if (!out_ll) return DGMM_ERR_BAD_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    Plan plan;
     Workspace ws;
-    rc = run_pair(MODE_LOGLIK, X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, nullptr, 0.f, out_ll, workspace,
-                  workspace_bytes, st, &plan, &ws);
+    int nblk = 0;
+    rc = loglik_pass(X, S, noise_layout, N, D, K, log_alpha, mu, Sigma, out_ll, workspace, workspace_bytes, st, &ws, &nblk);
     if (rc) return rc;
     if (N > 0 && (out_log_r || out_b || out_B)) {
         FullParams f;
@@ -754,7 +1086,7 @@ int dgmm_estep_full_f32(const float* X, const float* S, int noise_layout, int64_
         CUDA_TRY(cudaLaunchKernel(k, dim3((unsigned)blocks), dim3(128), args, 0, st));
     }
     if (status) {
-        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, plan.grid, nullptr, status, 0);
+        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, nblk, nullptr, status, 0);
         CUDA_TRY(cudaGetLastError());
     }
     return 0;
@@ -992,16 +1324,10 @@ static int stats_pass_host(dgmm_ctx* c, const float* X, const float* S, int layo
     const int D = c->D, K = c->K;
     cudaStream_t st = c->comp_st;
     CUDA_TRY(cudaMemsetAsync(c->d_stats, 0, dgmm_stats_len(D, K) * 4, st));
-    return stream_chunks(c, X, S, layout, N, [&](int, int64_t, int64_t n, const float* dX, const float* dS) -> int {
-        Plan plan;
-        Workspace ws;
-        int r = run_pair(MODE_STATS, dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr,
-                         resp_floor, nullptr, c->ws, c->ws_bytes, st, &plan, &ws);
-        if (r) return r;
-        finalize_stats_kernel<<<ns_of(D) * ((K + 31) / 32) + 1, dim3(32, kFinY), 0, st>>>(ws.part, ws.part_ll, ws.nonpd, plan.grid, D, K,
-                                                                   plan.GS, (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.TPB : plan.GS,
-                                                                   (plan.accp == ST_GLOBAL || plan.accp == ST_TMEM) ? plan.NSLOT : 1, c->d_stats, 1);
-        return (int)cudaGetLastError();
+    return stream_chunks(c, X, S, layout, N, [&](int idx, int64_t, int64_t n, const float* dX, const float* dS) -> int {
+        // (d_ll: scratch of the cooperative path, D > 16; ordered on `st` like everything else of the chunk)
+        return stats_pass(dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr, resp_floor,
+                          c->d_ll[idx & 1], c->d_stats, 1, c->ws, c->ws_bytes, st);
     });
 }
 
@@ -1060,12 +1386,12 @@ int dgmm_score_host(dgmm_ctx* c, const float* X, const float* S, int layout, int
     CUDA_TRY(cudaMemsetAsync(c->d_sum, 0, 2 * sizeof(double), st));
     int rc = stream_chunks(c, X, S, layout, N, [&](int idx, int64_t off, int64_t n, const float* dX, const float* dS) -> int {
         float* dll = c->d_ll[idx & 1];  // safe to reuse: its D2H copy two chunks ago is ordered on `st`
-        Plan plan;
         Workspace ws;
-        int r = run_pair(MODE_LOGLIK, dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr, 0.f, dll,
-                         c->ws, c->ws_bytes, st, &plan, &ws);
+        int nblk = 0;
+        int r = loglik_pass(dX, dS, layout, n, D, K, c->d_log_alpha, c->d_mu, c->d_Sigma, dll, c->ws, c->ws_bytes, st, &ws,
+                            &nblk);
         if (r) return r;
-        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, plan.grid, c->d_sum, nullptr, 1);
+        finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, nblk, c->d_sum, nullptr, 1);
         CUDA_TRY(cudaGetLastError());
         if (out_ll) CUDA_TRY(cudaMemcpyAsync(out_ll + off, dll, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
         return 0;

@@ -227,10 +227,3 @@ namespace unrolled {
 }  // namespace dgmm
 #undef DGMM_LOOP
 
-#define DGMM_LOOP _Pragma("unroll 4")
-namespace dgmm {
-namespace rolled {
-#include "dgmm_pair_body.inc"
-}  // namespace rolled
-}  // namespace dgmm
-#undef DGMM_LOOP

@@ -23,11 +23,9 @@ typedef const void* (*full_lookup_fn)();
 
 template <int D, int MODE, int SIGP, int ACCP, int GCLS, int NZ, int MAXT, int MINB>
 inline PairVariant pair_variant() {
+    static_assert(D <= DGMM_UNROLL_D, "thread-per-pair kernels above D = 16 exist only as pair_variant_wide_unrolled");
     PairVariant v;
-    if constexpr (D <= DGMM_UNROLL_D)
-        v.fn = reinterpret_cast<const void*>(&unrolled::pair_kernel<D, MODE, SIGP, ACCP, GCLS, NZ, MAXT, MINB>);
-    else
-        v.fn = reinterpret_cast<const void*>(&rolled::pair_kernel<D, MODE, SIGP, ACCP, GCLS, NZ, MAXT, MINB>);
+    v.fn = reinterpret_cast<const void*>(&unrolled::pair_kernel<D, MODE, SIGP, ACCP, GCLS, NZ, MAXT, MINB>);
     v.sigp = SIGP; v.accp = ACCP; v.gcls = GCLS; v.nz = NZ; v.max_threads = MAXT; v.min_blocks = MINB;
     return v;
 }
@@ -91,13 +89,18 @@ inline PairVariant pair_by_gcls(int gcls, int nz) {
 //   LOGLIK       : Sigma_j in shared-memory columns; 128 registers x 4 blocks/SM (D <= 12), 255 above
 //   D = 17..24   : K >= 64: as 13..16 (unrolled, a few spilled words; Sigma_j through L1 when its columns
 //                  would leave one block per SM, and for K > 128); otherwise the fallback
-//   D > 24       : fallback only (rolled loops, local-memory arrays)
+//   D = 21..32, and D = 17..20 with K < 64: the cooperative 8-lane-team kernels (dgmm_team.cuh)
 template <int D>
 inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
     if (which == 2) {
-        if (mode == MODE_LOGLIK)
-            return pair_variant<D, MODE_LOGLIK, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
-        return pair_variant<D, MODE_STATS, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
+        // universal fallback of the thread-per-pair family; above D = 16 the cooperative kernels
+        // (dgmm_team.cuh) serve everything the unrolled variants do not
+        if constexpr (D <= DGMM_UNROLL_D) {
+            if (mode == MODE_LOGLIK)
+                return pair_variant<D, MODE_LOGLIK, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
+            return pair_variant<D, MODE_STATS, ST_GLOBAL, ST_GLOBAL, GCLS_ANY, NZ_ANY, kPairMaxThreads, 1>();
+        }
+        return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
     }
     if (which == 1) {  // alternative placements (tuning sweeps, tools/gpu_ab.sh)
         if constexpr (D <= 12) {

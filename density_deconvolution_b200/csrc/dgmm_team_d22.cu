@@ -1,0 +1,3 @@
+// Instantiates the cooperative (team) kernels for D = 22 (see dgmm_team.cuh).
+#include "dgmm_team.cuh"
+DGMM_DEFINE_TEAM_DIM(22)

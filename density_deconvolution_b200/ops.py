@@ -47,6 +47,19 @@ def workspace(D, K, device):
     return ws
 
 
+_ll_scratches = {}
+
+
+def _ll_scratch(N, device):
+    """[N] float32 scratch for the D > 16 statistics pass (grown on demand, one per device)."""
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    t = _ll_scratches.get(key)
+    if t is None or t.numel() < N:
+        t = torch.empty(max(N, 1), dtype=torch.float32, device=device)
+        _ll_scratches[key] = t
+    return t[:N]
+
+
 def _noise(S, layout, N, D, device):
     code = NOISE_LAYOUTS[layout] if isinstance(layout, str) else int(layout)
     if code == _lib.NOISE_NONE:
@@ -104,6 +117,8 @@ def estep_stats(X, S, log_alpha, mu, Sigma, g=None, resp_floor=0.0, noise="full"
         if g.numel() != N:
             raise ValueError("g must have N elements")
     ll = torch.empty(N, dtype=torch.float32, device=dev) if want_ll else None
+    if ll is None and D > 16 and _lib.lib().dgmm_stats_needs_ll(D, K, code):
+        ll = _ll_scratch(N, dev)      # the two-pass cooperative path carries ll_i between its passes
     if out_stats is None:
         out_stats = torch.empty(stats_len(D, K), dtype=torch.float32, device=dev)
     ws = workspace(D, K, dev)
@@ -112,7 +127,7 @@ def estep_stats(X, S, log_alpha, mu, Sigma, g=None, resp_floor=0.0, noise="full"
                                              _ptr(g), float(resp_floor), _ptr(ll), _ptr(out_stats), _ptr(ws),
                                              ws.numel(), _stream(dev))
     check(rc, "dgmm_estep_stats_f32")
-    return ll, out_stats
+    return (ll if want_ll else None), out_stats
 
 
 def estep_full(X, S, log_alpha, mu, Sigma, noise="full", want_means=True, want_covars=True):

@@ -52,6 +52,7 @@ extern "C" {
 #define DGMM_ERR_WORKSPACE (-4)      /* workspace too small / null                      */
 #define DGMM_ERR_LAYOUT (-5)         /* unknown noise layout                            */
 #define DGMM_ERR_NO_DEVICE (-6)      /* no CUDA device / not an sm_100 part             */
+#define DGMM_ERR_LL_REQUIRED (-7)    /* dgmm_estep_stats_f32 needs out_ll for this shape (dgmm_stats_needs_ll) */
 
 /* noise-covariance layouts (the reference contract is DGMM_NOISE_FULL:
  * deconv/gmm/data.py:7-17, deconv/gmm/sgd_deconv_gmm.py:31-41) */
@@ -83,6 +84,11 @@ DGMM_API int dgmm_supported_dims(int* list, int* n);
  * dgmm_estep_full_f32 for this shape on the current device (0 on error). */
 DGMM_API size_t dgmm_workspace_bytes(int D, int K);
 
+/* 1 when dgmm_estep_stats_f32 needs a non-NULL out_ll [N] for this shape: above D = 16 the statistics run as
+ * two passes (cooperative 8-lane teams per pair, csrc/dgmm_team.cuh) and ll_i travels from the first to the
+ * second through out_ll.  0 otherwise (out_ll optional). */
+DGMM_API int dgmm_stats_needs_ll(int D, int K, int noise_layout);
+
 /* ---- device entry points ------------------------------------------------------------ */
 
 /* Per-point log-likelihood  ll_i = log sum_j alpha_j N(x_i | mu_j, Sigma_j + S_i).
@@ -102,7 +108,8 @@ DGMM_API int dgmm_loglik_f32(const float* X, const float* S, int noise_layout, i
  * autograd backward of deconv/gmm/sgd_deconv_gmm.py:14-28 (deconv/gmm/sgd_gmm.py:181).
  *   g [N] optional per-point weights (NULL = 1; = grad_output for the SGD backward);
  *   resp_floor: 0 for EM/SGD, 10*eps for OnlineDeconvGMM (online_deconv_gmm.py:150);
- *   out_ll [N] optional; out_stats [dgmm_stats_len(D,K)]. */
+ *   out_ll [N] optional (required where dgmm_stats_needs_ll says so: DGMM_ERR_LL_REQUIRED otherwise);
+ *   out_stats [dgmm_stats_len(D,K)]. */
 DGMM_API int dgmm_estep_stats_f32(const float* X, const float* S, int noise_layout, int64_t N, int D, int K,
                          const float* log_alpha, const float* mu, const float* Sigma,
                          const float* g, float resp_floor,

@@ -134,6 +134,22 @@ def suff_stats(X, S, alpha, mu, Sigma, g=None, resp_floor=0.0, dtype=np.float64)
     return s0, s1, S2, ll
 
 
+def suff_stats_scales(X, S, alpha, mu, Sigma, g=None, resp_floor=0.0, dtype=np.float64):
+    """Per-component magnitudes of the sums behind ``suff_stats`` (test infrastructure: the natural
+    error scale of a float32 accumulation of each component's statistics, also where the signed sum
+    cancels): ``A1_j = sum_i |omega_ij| |u_ij|`` ``[K,D]``, ``A2_j = sum_i |omega_ij| (|u u^T| + |T^{-1}|)``
+    ``[K,D,D]``."""
+    lp, t = log_joint(X, S, alpha, mu, Sigma, dtype)
+    ll = _logsumexp(lp, axis=1)
+    om = np.abs(np.exp(lp - ll[:, None]) + resp_floor)
+    if g is not None:
+        om = om * np.abs(np.asarray(g, dtype=dtype))[:, None]
+    u = np.abs(t["u"])
+    A1 = np.einsum("nk,nkd->kd", om, u)
+    A2 = np.einsum("nk,nkab->kab", om, u[..., :, None] * u[..., None, :] + np.abs(t["T_inv"]))
+    return A1, A2
+
+
 def m_step_from_stats(s0, s1, S2, mu, Sigma, n_total, w, dtype=np.float64):
     """EM update written on the fused statistics.
 

@@ -372,6 +372,99 @@ def posterior_sample_case(name, N=4, D=3, K=4, M=60000):
     print(name, mean, lp3.shape, lp2.shape)
 
 
+def real_noise(seed, N, D):
+    """Per-point full noise for the real tables (regenerated from the seed by the tests, not stored):
+    S_i = Q_i^T Q_i + 1e-3 I with Q_i ~ (0.5 / sqrt(D)) N(0,1)^{DxD} (experiments/gmm/checks/data.py:9-10
+    scaled so that trace(S_i)/D ~ 0.25 on standardised columns)."""
+    rng = np.random.default_rng(seed)
+    Q = (0.5 / np.sqrt(D)) * rng.standard_normal((N, D, D))
+    S = np.einsum("nba,nbc->nac", Q, Q) + 1e-3 * np.eye(D)
+    L = np.linalg.cholesky(S)
+    noise = np.einsum("nab,nb->na", L, rng.standard_normal((N, D)))
+    return S, noise
+
+
+def tril_pack(C):
+    D = C.shape[-1]
+    ia, ib = np.tril_indices(D)
+    return C[..., ia, ib]
+
+
+def real_em_case(name, X0, K, iters, seed, w=1e-3, sgd=None):
+    """EM from the reference's own style of injected init (alpha = 1/K, mu = K distinct rows, Sigma = I:
+    deconv/gmm/util.py:42, online_deconv_gmm.py:32-36) on a real table with synthetic per-point full
+    noise; float64 reference, parameters stored as float32 lower triangles after the listed iteration counts."""
+    dtype = torch.float64
+    torch.set_default_dtype(dtype)
+    N, D = X0.shape
+    S, noise = real_noise(seed, N, D)
+    X = X0 + noise
+    rng = np.random.default_rng(seed + 1)
+    rows = np.sort(rng.choice(N, size=K, replace=False))
+    m = DeconvGMM(K, D, w=w)
+    inject(m, np.full(K, 1.0 / K), X[rows].copy(), np.tile(np.eye(D), (K, 1, 1)), dtype)
+    data = (torch.tensor(X), torch.tensor(S))
+    out = dict(X=X.astype(np.float32), X64=X, rows=rows, w=w, seed=seed, K=K)
+    lls = []
+    for it in range(1, max(iters) + 1):
+        ll, e = m._e_step(data)
+        lls.append(ll.item())
+        m._m_step(data, e)
+        del e
+        if it in iters:
+            out["it%d_weights" % it] = m.weights.numpy().reshape(-1).astype(np.float32)
+            out["it%d_means" % it] = m.means.numpy().astype(np.float32)
+            out["it%d_covars_tril" % it] = tril_pack(m.covars.numpy()).astype(np.float32)
+        print(name, "iteration", it, "ll", lls[-1], flush=True)
+    out["ll_trace"] = np.asarray(lls)
+    if sgd is not None:
+        # a short SGD trajectory of the reference's module / reg_loss / Adam from the same init, batches in order
+        epochs, batch, lr = sgd
+        sg = SGDDeconvGMM(K, D, w=w, batch_size=batch, lr=lr)
+        sg.module.soft_weights.data = torch.zeros(K, dtype=dtype)
+        sg.module.means.data = torch.tensor(X[rows].copy())
+        sg.module.l_diag.data = torch.zeros(K, D, dtype=dtype)
+        sg.module.l_lower.data = torch.zeros(K, D * (D - 1) // 2, dtype=dtype)
+        tX, tS = data
+        curve = []
+        for ep in range(epochs):
+            tot = 0.0
+            for lo in range(0, N, batch):
+                d = [tX[lo:lo + batch], tS[lo:lo + batch]]
+                sg.optimiser.zero_grad()
+                lp = sg.module(d)
+                loss = -1 * torch.mean(lp)
+                tot += torch.sum(lp).item()
+                loss += sg.reg_loss(d[0].shape[0], N)
+                loss.backward()
+                sg.optimiser.step()
+            curve.append(tot / N)
+            sg.scheduler.step()
+            print(name, "sgd epoch", ep, curve[-1], flush=True)
+        out["sgd_epochs"], out["sgd_batch"], out["sgd_lr"] = epochs, batch, lr
+        out["sgd_curve"] = np.asarray(curve)
+        for pn in ("soft_weights", "means", "l_diag", "l_lower"):
+            out["sgd_" + pn] = getattr(sg.module, pn).detach().numpy().astype(np.float32)
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, lls)
+
+
+def ionosphere_case(name):
+    """BASELINE.json configs[3] / SURVEY.md 8d item 4: ionosphere (351x32), K = 256, full noise, injected
+    init, 5 EM iterations, w = 1e-3."""
+    X0 = np.load(os.path.join(REF, "data_small", "ionosphere_no_discrete_no_corr_0.98.npy"))
+    real_em_case(name, X0, K=256, iters=(1, 5), seed=4004)
+
+
+def wine_case(name):
+    """BASELINE.json configs[2]: white + red wine (6497x9), K = 128, full noise, injected init, parameters
+    after 1 / 5 / 20 EM iterations and a 2-epoch SGD trajectory."""
+    X0 = np.concatenate([np.load(os.path.join(REF, "data_small", "white_no_discrete_no_corr_0.98.npy")),
+                         np.load(os.path.join(REF, "data_small", "red_no_discrete_no_corr_0.98.npy"))])
+    real_em_case(name, X0, K=128, iters=(1, 5, 20), seed=3003, sgd=(2, 500, 1e-3))
+
+
 def main():
     if len(sys.argv) > 1 and sys.argv[1] == "posterior_sample":
         posterior_sample_case("ref_posterior_sample.npz")
@@ -379,6 +472,12 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "sgd_fit":
         sgd_fit_case("ref_sgd_fit_d5_k3_f32.npz", N=64, D=5, K=3, dtype=torch.float32)
         sgd_fit_case("ref_sgd_fit_d3_k4_f64.npz", N=48, D=3, K=4, dtype=torch.float64)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "ionosphere":
+        ionosphere_case("ref_ionosphere_k256_f64.npz")
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "wine":
+        wine_case("ref_wine_k128_f64.npz")
         return
     if len(sys.argv) > 1 and sys.argv[1] == "kmeans":
         kmeans_case("ref_kmeans.npz")
@@ -399,6 +498,8 @@ def main():
     sgd_fit_case("ref_sgd_fit_d5_k3_f32.npz", N=64, D=5, K=3, dtype=torch.float32)
     sgd_fit_case("ref_sgd_fit_d3_k4_f64.npz", N=48, D=3, K=4, dtype=torch.float64)
     posterior_sample_case("ref_posterior_sample.npz")
+    ionosphere_case("ref_ionosphere_k256_f64.npz")
+    wine_case("ref_wine_k128_f64.npz")
 
 
 if __name__ == "__main__":

@@ -27,6 +27,17 @@ def to_dev(*arrs):
     return [torch.tensor(np.ascontiguousarray(a), dtype=torch.float32, device=dev()) for a in arrs]
 
 
+def check_stats_per_component(d0, d1, d2, s0, s1, S2, A1, A2, rtol=STAT_RTOL):
+    """Every component on its own scale: a small component must be right too (the global checks above
+    are relative to the LARGEST entry).  A1 / A2 are the absolute sums behind s1 / S2 (their float32
+    accumulation error scales with them, also where the signed sum cancels)."""
+    assert np.all(np.abs(d0 - s0) <= rtol * s0 + 1e-30), np.max(np.abs(d0 - s0) / (s0 + 1e-300))
+    e1 = np.abs(d1 - s1).max(axis=1) / (A1.max(axis=1) + 1e-300)
+    e2 = np.abs(d2 - S2).max(axis=(1, 2)) / (A2.max(axis=(1, 2)) + 1e-300)
+    assert e1.max() <= rtol, ("s1", int(e1.argmax()), float(e1.max()))
+    assert e2.max() <= rtol, ("S2", int(e2.argmax()), float(e2.max()))
+
+
 def run_case(ops, N, D, K, seed, noise="full", with_g=False, floor=0.0):
     rng = np.random.default_rng(seed)
     X, S, alpha, mu, Sigma = synth(rng, N, D, K)
@@ -61,6 +72,8 @@ def run_case(ops, N, D, K, seed, noise="full", with_g=False, floor=0.0):
     assert abs((tail[0] + tail[1]) - ll.sum()) <= LL_RTOL * abs(ll.sum())
     assert abs(tail[2] - (g.sum() if with_g else N)) <= 1e-5 * N
     assert tail[3] == 0
+    A1, A2 = orc.suff_stats_scales(X, S_or, alpha, mu, Sigma, g=g, resp_floor=floor)
+    check_stats_per_component(d0, d1, d2, s0, s1, S2, A1, A2)
     return dict(X=X, S=S_or, alpha=alpha, mu=mu, Sigma=Sigma, stats=stats, s=(s0, s1, S2), ll=ll)
 
 
@@ -77,7 +90,8 @@ def test_dims_unrolled(ops, D):
 
 
 @pytest.mark.parametrize("D", [17, 24, 32])
-def test_dims_rolled(ops, D):
+def test_dims_above_16_small_k(ops, D):
+    """D > 16 with few components: the cooperative team kernels (tests/test_team_kernels.py has the sweep)."""
     run_case(ops, N=67, D=D, K=4, seed=200 + D)
 
 
@@ -87,10 +101,14 @@ def test_dims_rolled(ops, D):
                                        (24, 64, "diag")])
 def test_dims_unrolled_with_spills(ops, D, K, noise):
     """D = 17..24 with 64+ components: the fully unrolled kernels (main placement, not the rolled fallback)."""
-    for mode in (0, 1):
-        plan = ops.get_plan(mode, D, K, 1000, noise=noise)
-        assert plan["rc"] in (0, 1), plan   # not the rolled fallback (rc == 2)
-    run_case(ops, N=203 if K <= 128 else 75, D=D, K=K, seed=250 + D + K, noise=noise, with_g=(D % 2 == 0))
+    ops.set_tuning(rc=4)     # the thread-per-pair family (D >= 21 goes to the team kernels by default)
+    try:
+        for mode in (0, 1):
+            plan = ops.get_plan(mode, D, K, 1000, noise=noise)
+            assert plan["rc"] in (0, 1), plan   # an unrolled placement, not the cooperative path (rc == 3)
+        run_case(ops, N=203 if K <= 128 else 75, D=D, K=K, seed=250 + D + K, noise=noise, with_g=(D % 2 == 0))
+    finally:
+        ops.set_tuning()
 
 
 @pytest.mark.parametrize("K", [1, 2, 3, 8, 10, 31, 32, 33, 64, 100, 128, 256])
