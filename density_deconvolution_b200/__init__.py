@@ -12,7 +12,8 @@ __all__ = ["DgmmError", "LIB_PATH", "build"]
 def __getattr__(name):
     # estimator classes import torch; keep `import density_deconvolution_b200` light
     if name in ("DeconvGMM", "OnlineDeconvGMM", "BatchDeconvGMM", "SGDDeconvGMM", "SGDDeconvGMMModule",
-                "SGDDeconvDataset", "DeconvDataset", "SGDGMM", "SGDGMMModule", "BaseSGDGMM"):
+                "SGDDeconvDataset", "DeconvDataset", "SGDGMM", "SGDGMMModule", "BaseSGDGMM",
+                "BaseSGDGMMTim", "SGDGMMTim", "SGDDeconvGMMTim"):
         from . import estimators
         return getattr(estimators, name)
     raise AttributeError(name)

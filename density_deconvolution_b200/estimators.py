@@ -67,6 +67,21 @@ def _global_count(n, device):
     return int(t.item())
 
 
+def _global_batch_sizes(loader):
+    """Global size of every minibatch the (rank-synchronised) loader will yield: the sum over ranks of
+    ``min(batch, n_r - b * batch)``.  Computed once per fit from an all-gather of the shard sizes, so the
+    per-step loss scale is right even when the ranks' last batches differ (``N % world_size != 0``)."""
+    nb, bs = len(loader), loader.batch_size
+    if _dist.is_distributed():
+        t = torch.zeros(_dist.world_size(), dtype=torch.int64, device=loader.device)
+        t[_dist.rank()] = loader.n
+        torch.distributed.all_reduce(t)
+        shard = t.tolist()
+    else:
+        shard = [loader.n]
+    return [sum(max(0, min(bs, n_r - b * bs)) for n_r in shard) for b in range(nb)]
+
+
 class _Mixture:
     """Device-resident ``(alpha, log_alpha, mu, Sigma)`` in the layout the C ABI takes."""
 
@@ -133,36 +148,51 @@ class DeconvGMM:
         cond_covars = torch.eye(self.d, device=self.device).expand(n, self.k, self.d, self.d)
         return (log_resps, cond_means, cond_covars)
 
-    def _init_from_labels(self, X, resps, centroids=None):
+    def _init_from_labels(self, X, labels, centroids=None):
         """The M-step the reference applies to the k-means expectations (cond_means = X,
-        cond_covars = I; deconv_gmm.py:21-34,81-109) without the ``[N,K,D,D]`` broadcast.
-        An empty cluster (NaN parameters in the reference) is seeded with one pseudo-point at
-        its centroid."""
+        cond_covars = I; deconv_gmm.py:21-34,81-109) from the hard LABELS: per-label sums by
+        ``index_add_`` over chunks of points, so neither the ``[N,K,D,D]`` broadcast of the reference nor
+        any ``[N,K,.]`` intermediate exists (N = 1e7 at the benchmark shapes).  An empty cluster (NaN
+        parameters in the reference) is seeded with one pseudo-point at its centroid."""
         n_total = _global_count(X.shape[0], self.device)
-        s0 = resps.sum(dim=0)                                          # [K]
-        sx = resps.t() @ X                                             # [K,D]
-        sxx = torch.einsum("nk,na,nb->kab", resps, X, X)               # [K,D,D]
+        if labels.dim() == 2:                                          # one-hot responsibilities
+            labels = labels.argmax(dim=1)
+        labels = labels.long()
+        d = self.d
+        s0 = torch.zeros(self.k, device=self.device, dtype=torch.float64)
+        sx = torch.zeros(self.k, d, device=self.device, dtype=torch.float64)
+        sxx = torch.zeros(self.k, d * d, device=self.device, dtype=torch.float64)
+        chunk = 1 << 20
+        for lo in range(0, X.shape[0], chunk):
+            xb = X[lo:lo + chunk].double()
+            lb = labels[lo:lo + chunk]
+            s0.index_add_(0, lb, torch.ones_like(lb, dtype=torch.float64))
+            sx.index_add_(0, lb, xb)
+            sxx.index_add_(0, lb, (xb[:, :, None] * xb[:, None, :]).reshape(-1, d * d))
+        sxx = sxx.view(self.k, d, d)
         if _dist.is_distributed():
             for t in (s0, sx, sxx):
                 torch.distributed.all_reduce(t)
         if centroids is not None:
             empty = s0 <= 0
+            c64 = centroids.double()
             s0 = torch.where(empty, torch.ones_like(s0), s0)
-            sx = torch.where(empty[:, None], centroids, sx)
-            sxx = torch.where(empty[:, None, None], centroids[:, :, None] * centroids[:, None, :], sxx)
+            sx = torch.where(empty[:, None], c64, sx)
+            sxx = torch.where(empty[:, None, None], c64[:, :, None] * c64[:, None, :], sxx)
         means = sx / s0[:, None]
-        eye = torch.eye(self.d, device=self.device)
+        eye = torch.eye(d, device=self.device, dtype=torch.float64)
         scatter = sxx - s0[:, None, None] * means[:, :, None] * means[:, None, :]
         covars = (scatter + s0[:, None, None] * eye + 2 * self.w_scalar * eye) / s0[:, None, None]
-        self.means, self.covars, self.weights = means, covars, (s0 / n_total)[:, None]
+        self.means, self.covars = means.float(), covars.float()
+        self.weights = (s0 / n_total)[:, None].float()
 
     # -- the hot loop (base.py:37-55) ---------------------------------------------------------
     def fit(self, data, init=True):
         X, S, layout = self._prep(data)
         n_total = _global_count(X.shape[0], self.device)
         if init:
-            resps, centroids = k_means(X, self.k, 50, 1e-9, self.device, ops=_ops)
-            self._init_from_labels(X, resps, centroids)
+            labels, centroids = k_means(X, self.k, 50, 1e-9, self.device, ops=_ops, return_labels=True)
+            self._init_from_labels(X, labels, centroids)
         mix = self._mixture()
         stats = torch.empty(_ops.stats_len(self.d, self.k), dtype=torch.float32, device=self.device)
         prev = -math.inf
@@ -227,7 +257,9 @@ class DeconvGMM:
         _, sums = _ops.loglik(X, S, mix.log_alpha, mix.mu, mix.Sigma, noise=layout, want_sum=True)
         if _dist.is_distributed():
             torch.distributed.all_reduce(sums)
-        return torch.where(sums[1] > 0, torch.full_like(sums[0], -math.inf), sums[0]).to(torch.float32)
+        # float64: at N ~ 1e6 the summed log-likelihood exceeds float32's integer range and two epochs would
+        # compare equal (a spurious "converged"); the reference accumulates per-batch .item() in a Python double
+        return torch.where(sums[1] > 0, torch.full_like(sums[0], -math.inf), sums[0])
 
     def score_samples(self, data):
         """Per-point log-likelihood ``[N]``."""
@@ -311,9 +343,10 @@ class OnlineDeconvGMM(DeconvGMM):
 
     def fit(self, data, val_data=None, verbose=False, interval=1, init=True):
         X, S, layout = self._prep(data)
-        loader = DeviceBatches((X, S), self.batch_size, self.device, shuffle=True, drop_last=True, ops=_ops)
+        loader = DeviceBatches((X, S), self.batch_size, self.device, shuffle=True, drop_last=True, ops=_ops).sync_ranks()
         if init:
-            init_loader = DeviceBatches((X, S), self.k_means_factor * self.batch_size, self.device, shuffle=True, ops=_ops)
+            init_loader = DeviceBatches((X, S), self.k_means_factor * self.batch_size, self.device, shuffle=True,
+                                        ops=_ops).sync_ranks()
             self._init_sum_stats(init_loader, X.shape[0])
         elif not hasattr(self, "sum_resps"):
             self._reset_running_sums()
@@ -385,7 +418,8 @@ class BatchDeconvGMM(OnlineDeconvGMM):
         X, S, layout = self._prep(data)
         n_total = _global_count(X.shape[0], self.device)
         if init:
-            init_loader = DeviceBatches((X, S), self.k_means_factor * self.batch_size, self.device, shuffle=True, ops=_ops)
+            init_loader = DeviceBatches((X, S), self.k_means_factor * self.batch_size, self.device, shuffle=True,
+                                        ops=_ops).sync_ranks()
             self._init_sum_stats(init_loader, X.shape[0])
         self.train_ll_curve = []
         if val_data:
@@ -528,23 +562,30 @@ class SGDGMMModule(nn.Module):
     def log_prob(self, data):
         return self.forward([data])
 
+    def _data(self, data):
+        """``(x, S, layout)`` of one minibatch: this module reads ``data[0]`` only (sgd_gmm.py:49-62)."""
+        return _resident(data[0], self.means.device), None, "none"
+
+    def log_prob_sum(self, data):
+        """``sum_i ll_i`` (all-reduced over ranks) with gradients from a single kernel pass."""
+        x, S, layout = self._data(data)
+        log_alpha, mu, Sigma = self._mixture_tensors()
+        return _DeconvLogLikSum.apply(x, S, log_alpha, mu, Sigma, layout)
+
 
 class SGDDeconvGMMModule(SGDGMMModule):
     """deconv/gmm/sgd_deconv_gmm.py:12-28: ``forward((x, noise_covars)) -> ll [B]``, differentiable
     w.r.t. ``soft_weights, means, l_diag, l_lower``."""
 
-    def forward(self, data):
+    def _data(self, data):
         x = _resident(data[0], self.means.device)
-        S = _resident(data[1], self.means.device)
-        log_alpha, mu, Sigma = self._mixture_tensors()
-        return _DeconvLogLik.apply(x, S, log_alpha, mu, Sigma, _noise_layout(x, S))
+        S = _resident(data[1], self.means.device) if data[1] is not None else None
+        return x, S, _noise_layout(x, S)
 
-    def log_prob_sum(self, data):
-        """``sum_i ll_i`` (all-reduced over ranks) with gradients from a single kernel pass."""
-        x = _resident(data[0], self.means.device)
-        S = _resident(data[1], self.means.device)
+    def forward(self, data):
+        x, S, layout = self._data(data)
         log_alpha, mu, Sigma = self._mixture_tensors()
-        return _DeconvLogLikSum.apply(x, S, log_alpha, mu, Sigma, _noise_layout(x, S))
+        return _DeconvLogLik.apply(x, S, log_alpha, mu, Sigma, layout)
 
 
 class BaseSGDGMM:
@@ -595,9 +636,12 @@ class BaseSGDGMM:
             self.module.l_diag.zero_()
             self.module.l_lower.zero_()
 
-    def _batches(self, data, shuffle):
+    def _batches(self, data, shuffle, batch_size=None):
         X, S = as_tensors(data)
-        return DeviceBatches((X, S), self.batch_size, self.device, shuffle=shuffle and self.shuffle, ops=_ops)
+        if not isinstance(self.module, SGDDeconvGMMModule):
+            S = None                                       # SGDGMM reads data[0] only (sgd_gmm.py:49-62)
+        return DeviceBatches((X, S), batch_size or self.batch_size, self.device, shuffle=shuffle and self.shuffle,
+                             ops=_ops).sync_ranks()
 
     # ---- fused optimiser step: no autograd graph, five launches per minibatch -------------------
     fused_step = True   # False: the autograd route (module.log_prob_sum -> loss.backward -> optimiser.step)
@@ -605,7 +649,7 @@ class BaseSGDGMM:
 
     def _fused_step_ok(self):
         g = self.optimiser.param_groups[0]
-        return (self.fused_step and isinstance(self.module, SGDDeconvGMMModule)
+        return (self.fused_step and isinstance(self.module, SGDGMMModule)
                 and isinstance(self.optimiser, torch.optim.Adam) and len(self.optimiser.param_groups) == 1
                 and not g.get("weight_decay") and not g.get("amsgrad") and not g.get("maximize"))
 
@@ -623,7 +667,7 @@ class BaseSGDGMM:
             states.append(st)
         return params, states
 
-    def _fused_epoch(self, loader, n_total, ws):
+    def _fused_epoch(self, loader, n_total, sizes):
         """One epoch of sgd_gmm.py:167-182 on the fused kernels: per minibatch ONE statistics pass
         (forward and backward of the loss), one all-reduce, one Adam step on the ``[K,.]`` parameters
         (``dgmm_sgd_adam_step_f32``).  Returns the epoch's mean log-likelihood (:183)."""
@@ -636,9 +680,9 @@ class BaseSGDGMM:
         log_alpha, Sigma = _ops.sgd_params(data[0], data[2], data[3])
         epoch_acc = torch.zeros(2, dtype=torch.float64, device=self.device)
         stats = None
-        for X_b, S_b in loader:
-            n = X_b.shape[0] * ws                                                # global minibatch
-            _, stats = _ops.estep_stats(X_b, S_b, log_alpha, data[1], Sigma, noise=_noise_layout(X_b, S_b),
+        for b, (X_b, S_b) in enumerate(loader):
+            n = sizes[b]                                                         # global minibatch
+            _, stats = _ops.estep_stats(X_b, S_b, log_alpha, data[1], Sigma, noise=loader.layout,
                                         want_ll=False, out_stats=stats)
             _dist.allreduce_stats(stats)
             step += 1
@@ -652,13 +696,23 @@ class BaseSGDGMM:
             return math.nan
         return acc[0].item() / n_total
 
+    # the `_tim` fork of the loop (deconv/gmm/sgd_gmm_tim.py:112-227) differs in bookkeeping only: see BaseSGDGMMTim
+    _tim = False
+
     def fit(self, data, val_data=None, verbose=False, interval=1, init=True):
+        return self._fit(data, val_data, verbose, interval, init)
+
+    def _fit(self, data, val_data, verbose, interval, init, logger=None, es_tl=None):
+        tim = self._tim
+        sign = -1.0 if tim else 1.0        # the fork tracks the LOSS (-mean ll, lower is better): sgd_gmm_tim.py:176,192,210
         loader = self._batches(data, shuffle=True)
         n_local = loader.n
         n_total = _global_count(n_local, self.device)
-        ws = _dist.world_size()
+        sizes = _global_batch_sizes(loader)
         if init:
-            self.init_params(loader)
+            # sgd_gmm.py:153 initialises from the training loader; the fork from ONE batch holding the whole
+            # table (sgd_gmm_tim.py:152-153)
+            self.init_params(self._batches(data, shuffle=True, batch_size=n_local) if tim else loader)
         self.train_loss_curve = []
         if val_data:
             self.val_loss_curve = []
@@ -667,12 +721,12 @@ class BaseSGDGMM:
         fused = self._fused_step_ok()
         for i in range(self.epochs):
             if fused:
-                train_loss = self._fused_epoch(loader, n_total, ws)
+                train_loss = self._fused_epoch(loader, n_total, sizes)
             else:
                 epoch_ll = torch.zeros((), dtype=torch.float64, device=self.device)
-                for d in loader:
+                for b, d in enumerate(loader):
                     self.optimiser.zero_grad(set_to_none=True)
-                    n = d[0].shape[0] * ws                                       # global minibatch
+                    n = sizes[b]                                                 # global minibatch
                     ll_sum = self.module.log_prob_sum(d)                         # sgd_gmm.py:173 (+ all-reduce)
                     loss = -ll_sum / n + self.reg_loss(n, n_total)               # :174-179
                     epoch_ll += ll_sum.detach()                                  # :176 without the per-batch sync
@@ -681,30 +735,39 @@ class BaseSGDGMM:
                 train_loss = epoch_ll.item() / n_total
             if math.isnan(train_loss):
                 raise ValueError("Sigma_j + S_i is not positive definite for some (point, component) pair")
-            self.train_loss_curve.append(train_loss)
+            self.train_loss_curve.append(sign * train_loss)
+            if tim and es_tl is not None and sign * train_loss < es_tl:          # sgd_gmm_tim.py:187-189
+                break
             if val_data:
                 val_loss = self.score_batch(val_data) / _global_count(len(val_data), self.device)
-                self.val_loss_curve.append(val_loss)
-            self.scheduler.step()
+                self.val_loss_curve.append(sign * val_loss)
+            if not tim:
+                self.scheduler.step()                                            # disabled in the fork (:195)
             if verbose and i % interval == 0:
                 if val_data:
-                    print("Epoch {}, Train Loss: {}, Val Loss :{}".format(i, train_loss, val_loss))
+                    msg = "Epoch {}, Train Loss: {}, Val Loss :{}".format(i, sign * train_loss, sign * val_loss)
                 else:
-                    print("Epoch {}, Loss: {}".format(i, train_loss))
+                    msg = "Epoch {}, Loss: {}".format(i, sign * train_loss)
+                if tim and logger is not None:
+                    logger.info(msg)                                             # :204,207
+                else:
+                    print(msg)
             if val_data:
-                if val_loss > best_val_loss:
+                if val_loss > best_val_loss:          # higher mean ll == lower loss of the fork (:210)
                     no_improvement_epochs, best_val_loss = 0, val_loss
                 else:
                     no_improvement_epochs += 1
                 if no_improvement_epochs > self.max_no_improvement:
                     print("No improvement in val loss for {} epochs. Early Stopping at {}".format(
-                        self.max_no_improvement, val_loss))
+                        self.max_no_improvement, sign * val_loss))
+                    if tim:
+                        return sign * best_val_loss                              # :221
                     break
-            if abs(train_loss - prev_loss) < self.tol:
+            if not tim and abs(train_loss - prev_loss) < self.tol:               # commented out in the fork (:223-227)
                 print("Training loss converged within tolerance at {}".format(train_loss))
                 break
             prev_loss = train_loss
-        return self
+        return None if tim else self
 
     def score(self, data):
         """Per-point log-likelihood ``[B]`` (sgd_gmm.py:225-226)."""
@@ -715,7 +778,10 @@ class BaseSGDGMM:
         X, S = as_tensors(dataset)
         with torch.no_grad():
             X = _resident(X, self.device)
-            S = _resident(S, self.device)
+            if S is None or not isinstance(self.module, SGDDeconvGMMModule):
+                S = None
+            else:
+                S = _resident(S, self.device)
             log_alpha, mu, Sigma = self.module._mixture_tensors()
             _, sums = _ops.loglik(X, S, log_alpha.contiguous(), mu.contiguous(), Sigma.contiguous(),
                                   noise=_noise_layout(X, S), want_sum=True)
@@ -817,3 +883,60 @@ class SGDDeconvGMM(BaseSGDGMM):
         """sgd_deconv_gmm.py:121-130."""
         with torch.no_grad():
             return self._sample_posterior(x, num_samples).to(device)
+
+
+# =========================================================================================
+# The `_tim` forks (deconv/gmm/sgd_gmm_tim.py, deconv/gmm/sgd_deconv_gmm_tim.py)
+# =========================================================================================
+class BaseSGDGMMTim(BaseSGDGMM):
+    """deconv/gmm/sgd_gmm_tim.py:65-259: the same module, loss and Adam step as ``BaseSGDGMM`` with the
+    fork's loop bookkeeping - ``fit(data, logger, val_data=None, verbose=False, interval=1, es_tl=None)``
+    (:112), curves hold the LOSS ``-mean ll`` (:176,192), k-means initialisation from one batch holding the
+    whole table (:152-153), no LR scheduler step (:195), no tolerance stop (:223-227), ``es_tl`` early stop on
+    the training loss (:187-189), messages to ``logger.info`` (:204,207), ``max_no_improvement=30`` (:68) and
+    ``best_val_loss`` returned on a validation early stop (:221)."""
+    _tim = True
+
+    def __init__(self, components, dimensions, epochs=10000, lr=1e-3, batch_size=64, tol=1e-6,
+                 max_no_improvement=30, k_means_factor=100, w=1e-6, k_means_iters=10, lr_step=5, lr_gamma=0.1,
+                 device=None):
+        BaseSGDGMM.__init__(self, components, dimensions, epochs=epochs, lr=lr, batch_size=batch_size, tol=tol,
+                            max_no_improvement=max_no_improvement, k_means_factor=k_means_factor, w=w,
+                            k_means_iters=k_means_iters, lr_step=lr_step, lr_gamma=lr_gamma, device=device)
+
+    def fit(self, data, logger=None, val_data=None, verbose=False, interval=1, es_tl=None, init=True):
+        return self._fit(data, val_data, verbose, interval, init, logger=logger, es_tl=es_tl)
+
+    def score(self, data):
+        with torch.no_grad():                                                    # sgd_gmm_tim.py:231-233
+            return self.module(data)
+
+
+class SGDGMMTim(BaseSGDGMMTim):
+    """deconv/gmm/sgd_gmm_tim.py:262-270."""
+
+    def __init__(self, components, dimensions, epochs=10000, lr=1e-3, batch_size=64, tol=1e-6, w=1e-3, device=None):
+        self.module = SGDGMMModule(components, dimensions, w, device)
+        BaseSGDGMMTim.__init__(self, components, dimensions, epochs=epochs, lr=lr, batch_size=batch_size, w=w,
+                               tol=tol, device=device)
+
+
+class SGDDeconvGMMTim(BaseSGDGMMTim, SGDDeconvGMM):
+    """deconv/gmm/sgd_deconv_gmm_tim.py:44-143 (``SGDDeconvGMM`` there): the posterior / sampling methods of
+    ``SGDDeconvGMM`` on the fork's fit loop, plus ``log_prob_prior`` (:81-97)."""
+
+    def __init__(self, components, dimensions, epochs=10000, lr=1e-3, batch_size=64, tol=1e-6, w=1e-3,
+                 k_means_factor=100, k_means_iters=10, lr_step=5, lr_gamma=0.1, device=None):
+        self.module = SGDDeconvGMMModule(components, dimensions, w, device)
+        BaseSGDGMMTim.__init__(self, components, dimensions, epochs=epochs, lr=lr, batch_size=batch_size, w=w,
+                               tol=tol, k_means_factor=k_means_factor, k_means_iters=k_means_iters,
+                               lr_step=lr_step, lr_gamma=lr_gamma, device=device)
+
+    def log_prob_prior(self, x, device=torch.device("cpu")):
+        """Log density of ``x [N,D]`` under the fitted NOISE-FREE mixture (sgd_deconv_gmm_tim.py:81-97; the
+        reference loops over components on the CPU): the ``S = 0`` layout of the log-likelihood kernel."""
+        with torch.no_grad():
+            X = _resident(x, self.device)
+            log_alpha, mu, Sigma = self.module._mixture_tensors()
+            ll = _ops.loglik(X, None, log_alpha.contiguous(), mu.contiguous(), Sigma.contiguous(), noise="none")
+        return ll.to(device)

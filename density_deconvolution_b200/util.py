@@ -26,7 +26,7 @@ def _from_rank0(t):
     return t
 
 
-def k_means(X, k, max_iters=50, tol=1e-9, device=None, generator=None, ops=None):
+def k_means(X, k, max_iters=50, tol=1e-9, device=None, generator=None, ops=None, return_labels=False):
     """Lloyd's k-means from uniformly drawn centroids in the bounding box
     (deconv/gmm/util.py:4-33).  Returns ``(one-hot resp [N,k] float, centroids [k,D])``.
     Deliberate fix: an empty cluster keeps its previous centroid
@@ -46,6 +46,8 @@ def k_means(X, k, max_iters=50, tol=1e-9, device=None, generator=None, ops=None)
         if prev is not None and abs(total - prev) < tol:
             break
         prev = total
+    if return_labels:
+        return labels, centroids
     resp = torch.zeros(n, k, device=X.device, dtype=X.dtype)
     resp[torch.arange(n, device=X.device), labels.long()] = 1.0
     return resp, centroids

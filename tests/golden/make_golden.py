@@ -372,6 +372,82 @@ def posterior_sample_case(name, N=4, D=3, K=4, M=60000):
     print(name, mean, lp3.shape, lp2.shape)
 
 
+def fit_api_case(name):
+    """END-TO-END ``fit`` of the reference's ``SGDGMM`` (deconv/gmm/sgd_gmm.py:264-272: data[0] only, no noise)
+    and of the ``_tim`` fork's ``SGDDeconvGMM`` (deconv/gmm/sgd_deconv_gmm_tim.py + sgd_gmm_tim.py:112-227) - the
+    reference's own loops INCLUDING their minibatch-k-means initialisation, scheduler / logger / early-stop
+    bookkeeping.  The only intervention: ``DataLoader`` is asked not to shuffle, so that the batch order (and with
+    it the k-means seeds = the first K rows) is reproducible."""
+    import logging
+    import torch.utils.data as data_utils
+    import deconv.gmm.sgd_gmm as ref_sgd
+    import deconv.gmm.sgd_gmm_tim as ref_tim
+    import deconv.gmm.sgd_deconv_gmm_tim as ref_dtim
+
+    real_loader = data_utils.DataLoader
+
+    class OrderedLoader(real_loader):
+        def __init__(self, *a, **kw):
+            kw["shuffle"] = False
+            super().__init__(*a, **kw)
+
+    rng = np.random.default_rng(777)
+    N, D, K = 96, 3, 3
+    centres = np.array([[-6.0, 0.0, 3.0], [5.0, 4.0, -2.0], [0.0, -7.0, 0.0]])
+    comp = np.arange(N) % K                       # the first K rows belong to K different clusters
+    qn = 0.3 * rng.standard_normal((N, D, D))
+    S = np.einsum("nba,nbc->nac", qn, qn) + 1e-2 * np.eye(D)
+    X = centres[comp] + rng.standard_normal((N, D)) + np.einsum(
+        "nab,nb->na", np.linalg.cholesky(S), rng.standard_normal((N, D)))
+    Xv = centres[comp[:48]] + rng.standard_normal((48, D))
+    Sv = S[:48]
+    out = dict(X=X.astype(np.float32), S=S.astype(np.float32), Xv=Xv.astype(np.float32), Sv=Sv.astype(np.float32))
+    tX, tS = torch.tensor(out["X"]), torch.tensor(out["S"])
+    tXv, tSv = torch.tensor(out["Xv"]), torch.tensor(out["Sv"])
+    data_utils.DataLoader = OrderedLoader
+    try:
+        # (1) SGDGMM.fit: plain GMM on X, validation set, scheduler milestones at [2, 7]
+        torch.manual_seed(0)
+        m = ref_sgd.SGDGMM(K, D, epochs=5, lr=2e-2, batch_size=16, w=1e-3)
+        m.k_means_iters = 3
+        m.fit(data_utils.TensorDataset(tX), val_data=data_utils.TensorDataset(tXv), verbose=False)
+        out["plain_train_curve"] = np.asarray(m.train_loss_curve)
+        out["plain_val_curve"] = np.asarray(m.val_loss_curve)
+        for pn in ("soft_weights", "means", "l_diag", "l_lower"):
+            out["plain_" + pn] = getattr(m.module, pn).detach().numpy().copy()
+        out["plain_score_batch"] = m.score_batch(data_utils.TensorDataset(tX))
+        # (2) the _tim fork: SGDDeconvGMM.fit(data, logger, val_data, verbose, interval, es_tl)
+        records = []
+
+        class Sink(logging.Handler):
+            def emit(self, rec):
+                records.append(rec.getMessage())
+        logger = logging.getLogger("dgmm_golden")
+        logger.setLevel(logging.INFO)
+        logger.addHandler(Sink())
+        t = ref_dtim.SGDDeconvGMM(K, D, epochs=4, lr=2e-2, batch_size=16, w=1e-3, k_means_iters=3)
+        ds = ref_dtim.SGDDeconvDataset(tX, tS)
+        ret = t.fit(ds, logger, val_data=ref_dtim.SGDDeconvDataset(tXv, tSv), verbose=True, interval=2)
+        out["tim_train_curve"] = np.asarray(t.train_loss_curve)
+        out["tim_val_curve"] = np.asarray(t.val_loss_curve)
+        out["tim_returned_none"] = ret is None
+        out["tim_n_messages"] = len(records)
+        out["tim_lr_final"] = t.optimiser.param_groups[0]["lr"]
+        for pn in ("soft_weights", "means", "l_diag", "l_lower"):
+            out["tim_" + pn] = getattr(t.module, pn).detach().numpy().copy()
+        # es_tl: stops after the first epoch whose training loss is below the threshold
+        t2 = ref_dtim.SGDDeconvGMM(K, D, epochs=50, lr=2e-2, batch_size=16, w=1e-3, k_means_iters=3)
+        thr = float(out["tim_train_curve"][1]) + 1e-6
+        t2.fit(ds, logger, es_tl=thr)
+        out["tim_es_tl"] = thr
+        out["tim_es_epochs"] = len(t2.train_loss_curve)
+        assert ref_tim.BaseSGDGMM is not ref_sgd.BaseSGDGMM
+    finally:
+        data_utils.DataLoader = real_loader
+    np.savez_compressed(os.path.join(HERE, name), **out)
+    print(name, out["plain_train_curve"], out["tim_train_curve"], out["tim_es_epochs"], records)
+
+
 def real_noise(seed, N, D):
     """Per-point full noise for the real tables (regenerated from the seed by the tests, not stored):
     S_i = Q_i^T Q_i + 1e-3 I with Q_i ~ (0.5 / sqrt(D)) N(0,1)^{DxD} (experiments/gmm/checks/data.py:9-10
@@ -473,6 +549,9 @@ def main():
         sgd_fit_case("ref_sgd_fit_d5_k3_f32.npz", N=64, D=5, K=3, dtype=torch.float32)
         sgd_fit_case("ref_sgd_fit_d3_k4_f64.npz", N=48, D=3, K=4, dtype=torch.float64)
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "fit_api":
+        fit_api_case("ref_fit_api.npz")
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "ionosphere":
         ionosphere_case("ref_ionosphere_k256_f64.npz")
         return
@@ -498,6 +577,7 @@ def main():
     sgd_fit_case("ref_sgd_fit_d5_k3_f32.npz", N=64, D=5, K=3, dtype=torch.float32)
     sgd_fit_case("ref_sgd_fit_d3_k4_f64.npz", N=48, D=3, K=4, dtype=torch.float64)
     posterior_sample_case("ref_posterior_sample.npz")
+    fit_api_case("ref_fit_api.npz")
     ionosphere_case("ref_ionosphere_k256_f64.npz")
     wine_case("ref_wine_k128_f64.npz")
 

@@ -289,6 +289,6 @@ def test_fit_from_kmeans_improves_likelihood(device):
     assert sg.train_loss_curve[-1] > sg.train_loss_curve[0]
     assert sg.sample_prior(7).shape == (7, 2)
     assert sg.sample_posterior((data[0][:5], data[1][:5]), 4).shape == (5, 4, 2)
-    assert sg.posterior_log_prob(data[0][:5], (data[0][:5], data[1][:5])).shape == (5, 1) or True
+    assert sg.posterior_log_prob(data[0][:5], (data[0][:5], data[1][:5])).shape == (5, 5)   # [len(x), N]
     state = sg.module.state_dict()
     assert set(state) == {"soft_weights", "means", "l_diag", "l_lower"}
