@@ -8,15 +8,17 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdgmm_b200.so")
+# DGMM_LIB: A/B runs of an experimental build of the same library (tools/gpu_ab_lib.sh); never a fallback
+LIB_PATH = os.environ.get("DGMM_LIB") or os.path.join(_HERE, "libdgmm_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
-NOISE_FULL, NOISE_DIAG, NOISE_NONE, NOISE_SHARED = 0, 1, 2, 3
-NOISE_LAYOUTS = {"full": NOISE_FULL, "diag": NOISE_DIAG, "none": NOISE_NONE, "shared": NOISE_SHARED}
-MAX_D, MAX_K = 32, 256
+NOISE_FULL, NOISE_DIAG, NOISE_NONE, NOISE_SHARED, NOISE_PACKED = 0, 1, 2, 3, 4
+NOISE_LAYOUTS = {"full": NOISE_FULL, "diag": NOISE_DIAG, "none": NOISE_NONE, "shared": NOISE_SHARED,
+                 "packed": NOISE_PACKED}
+MAX_D, MAX_K = 32, 1024
 
 _ERRORS = {
-    -1: "bad argument", -2: "unsupported dimension D (1..32)", -3: "unsupported component count K (1..256)",
+    -1: "bad argument", -2: "unsupported dimension D (1..32)", -3: "unsupported component count K (1..1024) for this call",
     -4: "workspace too small", -5: "unknown noise layout", -6: "no sm_100 CUDA device",
     -7: "out_ll is required for this shape (dgmm_stats_needs_ll)",
 }
@@ -27,8 +29,10 @@ SYMBOLS = (
     "dgmm_estep_stats_f32", "dgmm_estep_full_f32", "dgmm_mstep_update_f32", "dgmm_online_mstep_f32",
     "dgmm_fp32_probe",
     "dgmm_ctx_create", "dgmm_ctx_destroy", "dgmm_em_iteration_host", "dgmm_estep_stats_host", "dgmm_score_host",
+    "dgmm_ctx_upload", "dgmm_em_iteration_resident", "dgmm_em_fit_resident", "dgmm_score_resident",
+    "dgmm_pack_noise_f32", "dgmm_pack_noise_host",
     "dgmm_kmeans_workspace_bytes", "dgmm_kmeans_assign_f32", "dgmm_kmeans_update_f32",
-    "dgmm_gather_points_f32", "dgmm_posterior_sample_f32", "dgmm_posterior_logprob_f32", "dgmm_sgd_params_f32", "dgmm_sgd_adam_step_f32",
+    "dgmm_gather_points_f32", "dgmm_posterior_sample_f32", "dgmm_posterior_logprob_f32", "dgmm_sgd_params_f32", "dgmm_sgd_adam_step_f32", "dgmm_sgd_fused_step_f32",
     "dgmm_debug_set_tuning", "dgmm_debug_get_plan", "dgmm_debug_pair_timing", "dgmm_debug_pair_times",
 )
 
@@ -96,6 +100,19 @@ def lib():
     L.dgmm_estep_stats_host.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp, f32, vp]
     L.dgmm_score_host.restype = i32
     L.dgmm_score_host.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp, vp, ctypes.POINTER(f64), ctypes.POINTER(i64)]
+    L.dgmm_ctx_upload.restype = i32
+    L.dgmm_ctx_upload.argtypes = [vp, vp, vp, i32, i64, i32]
+    L.dgmm_em_iteration_resident.restype = i32
+    L.dgmm_em_iteration_resident.argtypes = [vp, f32, vp, vp, vp, ctypes.POINTER(f64), ctypes.POINTER(i64)]
+    L.dgmm_em_fit_resident.restype = i32
+    L.dgmm_em_fit_resident.argtypes = [vp, i32, f32, f64, vp, vp, vp, ctypes.POINTER(i32), ctypes.POINTER(f64),
+                                       ctypes.POINTER(i64)]
+    L.dgmm_score_resident.restype = i32
+    L.dgmm_score_resident.argtypes = [vp, vp, vp, vp, vp, ctypes.POINTER(f64), ctypes.POINTER(i64)]
+    L.dgmm_pack_noise_f32.restype = i32
+    L.dgmm_pack_noise_f32.argtypes = [vp, i64, i32, vp, vp]
+    L.dgmm_pack_noise_host.restype = i32
+    L.dgmm_pack_noise_host.argtypes = [vp, i64, i32, vp]
     L.dgmm_kmeans_workspace_bytes.restype = sz
     L.dgmm_kmeans_workspace_bytes.argtypes = [i32, i32]
     L.dgmm_kmeans_assign_f32.restype = i32
@@ -115,6 +132,10 @@ def lib():
     L.dgmm_sgd_adam_step_f32.restype = i32
     L.dgmm_sgd_adam_step_f32.argtypes = [vp, f64, f64, f32, f32, f32, f32, f32, i32, i32, i32, vp, vp, vp, vp,
                                          ctypes.POINTER(vp), ctypes.POINTER(vp), vp, vp, vp, vp]
+    L.dgmm_sgd_fused_step_f32.restype = i32
+    L.dgmm_sgd_fused_step_f32.argtypes = [vp, vp, i32, i32, i32, vp, i64, i64, vp, vp, vp, i32, vp, f64, f64, f32, f32,
+                                          f32, f32, f32, i32, vp, vp, vp, vp, ctypes.POINTER(vp), ctypes.POINTER(vp),
+                                          vp, vp, vp, vp, sz, vp]
     L.dgmm_debug_set_tuning.restype = i32
     L.dgmm_debug_set_tuning.argtypes = [i32] * 8
     L.dgmm_debug_get_plan.restype = i32
@@ -123,7 +144,7 @@ def lib():
     L.dgmm_debug_pair_timing.argtypes = [i32]
     L.dgmm_debug_pair_times.restype = i32
     L.dgmm_debug_pair_times.argtypes = [ctypes.POINTER(f32), ctypes.POINTER(i32)]
-    if L.dgmm_abi_version() != 1:
+    if L.dgmm_abi_version() != 2:
         raise DgmmError("libdgmm_b200.so ABI version mismatch")
     _lib = L
     return L

@@ -9,6 +9,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <thread>
 #include <vector>
 
 #include "../../include/dgmm_b200.h"
@@ -424,7 +425,9 @@ struct Tuning {
     // (0 = main, 1 = alternative); the rest override the tile geometry.  -1 = automatic.
     int sigp = -1, accp = -1, nslot = -1, pt = -1, nst = -1, blocks_per_sm = -1, rc = -1, no_bulk = 0;
 };
-Tuning g_tuning;
+// Diagnostics state is per host thread: two estimators driven from two threads (each on its own stream) do not
+// see each other's tuning overrides or timing records.
+thread_local Tuning g_tuning;
 
 struct Plan {
     const void* kernel = nullptr;
@@ -437,7 +440,7 @@ size_t pair_smem_bytes(int D, int noise, bool has_g, int sigp, int accp, int GS,
                        int mode, int nz) {
     const StageLayout SL = stage_layout(D, noise, PT, has_g);
     size_t b = kSmemHeader + (size_t)NST * SL.bytes;
-    if (repack_noise(D, nz)) b += (size_t)PT * D * ((D + 3) & ~3) * 4;   // re-packed lower triangles of the tile
+    b += (size_t)PT * repack_floats_per_point(D, nz) * 4;   // re-packed lower triangles of the tile
     if (sigp == ST_SMEM) b += (size_t)pad_col(nd_of(D)) * GS * 4;
     if (mode == MODE_STATS && accp == ST_SMEM) b += (size_t)pad_col(ns_of(D)) * TPB * 4;
     if (mode == MODE_LOGLIK) b += (size_t)2 * PT * (GS + 16) * 4;  // deferred logsumexp rows
@@ -501,7 +504,7 @@ int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int no
     const bool force_fallback = (t.sigp == ST_GLOBAL && t.accp == ST_GLOBAL);
     int which = (t.rc == 1 || t.rc == 2) ? t.rc : 0;   // rc = 3 / 4 choose between the kernel families (use_team_path)
     PairVariant v{nullptr, 0, 0, 0, 0, 0, 0};
-    const int nz = (noise == NOISE_FULL) ? NZ_FULL : NZ_DIAG;
+    const int nz = (noise == NOISE_FULL) ? NZ_FULL : (noise == NOISE_PACKED ? NZ_PACKED : NZ_DIAG);
     bool ok = false;
     if (!force_fallback) {
         v = kDims[D].pair(mode, which, p.gcls, nz);
@@ -560,8 +563,8 @@ int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int no
     grid = std::min<long long>(grid, std::max<long long>(p.n_tiles, 1));
     p.grid = (int)grid;
 
-    const bool aligned = (((uintptr_t)X | (uintptr_t)(noise == NOISE_FULL || noise == NOISE_DIAG ? S : nullptr) |
-                           (uintptr_t)g) & 15) == 0;
+    const bool per_point = noise == NOISE_FULL || noise == NOISE_DIAG || noise == NOISE_PACKED;
+    const bool aligned = (((uintptr_t)X | (uintptr_t)(per_point ? S : nullptr) | (uintptr_t)g) & 15) == 0;
     p.use_bulk = (aligned && !t.no_bulk) ? 1 : 0;
     *out = p;
     return 0;
@@ -571,7 +574,7 @@ int check_common(const void* X, const void* S, int noise, int64_t N, int D, int 
                  const void* Sg) {
     if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
     if (K < 1 || K > DGMM_MAX_K) return DGMM_ERR_UNSUPPORTED_K;
-    if (noise < 0 || noise > 3) return DGMM_ERR_LAYOUT;
+    if (noise < 0 || noise > 4) return DGMM_ERR_LAYOUT;
     if (N < 0 || !la || !mu || !Sg) return DGMM_ERR_BAD_ARG;
     if (N > 0 && !X) return DGMM_ERR_BAD_ARG;
     if (N > 0 && noise != NOISE_NONE && !S) return DGMM_ERR_BAD_ARG;
@@ -587,7 +590,7 @@ struct PairTiming {
     cudaEvent_t a[kRing], b[kRing];
     bool made = false;
 };
-PairTiming g_timing;
+thread_local PairTiming g_timing;
 
 int timing_begin(cudaStream_t st) {
     if (!g_timing.on) return -1;
@@ -718,7 +721,7 @@ struct TeamPlan {
 bool use_team_path(int D, int K, int mode, int noise) {
     if (D <= 16) return false;
     if (g_tuning.rc == 3) return true;
-    const int nz = (noise == NOISE_FULL) ? NZ_FULL : NZ_DIAG;
+    const int nz = (noise == NOISE_FULL) ? NZ_FULL : (noise == NOISE_PACKED ? NZ_PACKED : NZ_DIAG);
     const PairVariant v = kDims[D].pair(mode, 0, group_class(group_size(K)), nz);
     if (!v.fn) return true;
     if (g_tuning.rc == 4) return false;
@@ -735,7 +738,7 @@ int make_team_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, i
     p.PT = t.pt > 0 ? ((t.pt + 3) & ~3) : 4;
     p.NST = t.nst > 0 ? std::min(t.nst, kMaxStages) : 2;
     const bool stats = (mode == MODE_STATS);
-    p.nz = (noise == NOISE_FULL || noise == NOISE_DIAG) ? team::TNZ_MATRIX : team::TNZ_NONE;
+    p.nz = (noise == NOISE_FULL || noise == NOISE_DIAG || noise == NOISE_PACKED) ? team::TNZ_MATRIX : team::TNZ_NONE;
     const TeamKernels tk = kTeam[D]();
     p.kernel = stats ? tk.stats[p.nz] : tk.loglik[p.nz];
     if (!p.kernel) return DGMM_ERR_UNSUPPORTED_D;
@@ -779,8 +782,8 @@ int make_team_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, i
         p.n_slices = 0;
         p.grid = (int)std::min<long long>(cap, std::max<long long>(p.n_tiles, 1));
     }
-    const bool aligned = (((uintptr_t)X | (uintptr_t)(noise == NOISE_FULL || noise == NOISE_DIAG ? S : nullptr) |
-                           (uintptr_t)g | (uintptr_t)ll) & 15) == 0;
+    const bool per_point = noise == NOISE_FULL || noise == NOISE_DIAG || noise == NOISE_PACKED;
+    const bool aligned = (((uintptr_t)X | (uintptr_t)(per_point ? S : nullptr) | (uintptr_t)g | (uintptr_t)ll) & 15) == 0;
     p.use_bulk = (aligned && !t.no_bulk) ? 1 : 0;
     *out = p;
     return 0;
@@ -896,9 +899,9 @@ int run_pair(int mode, const float* X, const float* S, int noise, int64_t N, int
 }
 
 // Log-likelihood pass on whichever kernel family serves (D, K); *nblk = per-block (sum ll) partials written.
-int loglik_pass(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
-                const float* mu, const float* Sigma, float* out_ll, void* workspace, size_t workspace_bytes,
-                cudaStream_t st, Workspace* ws_out, int* nblk) {
+int loglik_pass_1(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+                  const float* mu, const float* Sigma, float* out_ll, void* workspace, size_t workspace_bytes,
+                  cudaStream_t st, Workspace* ws_out, int* nblk) {
     if (use_team_path(D, K, MODE_LOGLIK, noise)) {
         DeviceInfo dev;
         int rc = device_info(&dev);
@@ -923,9 +926,9 @@ int loglik_pass(const float* X, const float* S, int noise, int64_t N, int D, int
 
 // Fused statistics pass + finalise into out_stats (beta = 1 accumulates) on whichever family serves (D, K).
 // The cooperative path needs ll_scratch [N] (it may be the caller's out_ll).
-int stats_pass(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
-               const float* mu, const float* Sigma, const float* g, float resp_floor, float* out_ll, float* out_stats,
-               int beta, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+int stats_pass_1(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+                 const float* mu, const float* Sigma, const float* g, float resp_floor, float* out_ll, float* out_stats,
+                 int beta, void* workspace, size_t workspace_bytes, cudaStream_t st) {
     if (use_team_path(D, K, MODE_STATS, noise)) {
         if (!out_ll) return DGMM_ERR_LL_REQUIRED;
         DeviceInfo dev;
@@ -951,6 +954,230 @@ int stats_pass(const float* X, const float* S, int noise, int64_t N, int D, int 
     return (int)cudaGetLastError();
 }
 
+
+// ---------------------------------------------------------------------------------------
+// K > 256: component chunks
+// ---------------------------------------------------------------------------------------
+// "Threads are components" caps one launch at 256 components.  Larger mixtures (the reference's Gaia runs use
+// K = 512: experiments/gmm/gaia/variable_k/fit_em.sh:18) are served in chunks of <= 256 components:
+//   pass 1  log-likelihood kernel per chunk c            -> ll_c[i] = log sum_{j in c} alpha_j N(.)
+//   combine ll_i = logsumexp_c ll_c[i],  g_c[i] = g_i exp(ll_c[i] - ll_i)
+//   pass 2  statistics kernel per chunk with weights g_c -> omega_ij = g_c[i] r^c_ij = g_i r_ij  (exact: the
+//           chunk-local responsibility times the chunk's share of the point is the global responsibility)
+// The chunk statistics are scattered into the caller's packed buffer, the tail comes from the combine kernel.
+// Cost: one extra log-likelihood pass (F_ll / F_em = 1/3 more flops than a single-launch E-step).  A
+// responsibility floor (Online EM's 10 eps) is applied as g_c[i] * floor, i.e. scaled by the chunk's share.
+// Scratch: (n_chunks + 1) N floats from the stream-ordered allocator (the only allocation the library makes
+// on the device-pointer API, and only for K > 256).
+constexpr int kChunkK = 256;
+struct KChunks {
+    int n, Kc;
+};
+inline KChunks k_chunks(int K) {
+    KChunks c;
+    c.n = (K + kChunkK - 1) / kChunkK;
+    c.Kc = (((K + c.n - 1) / c.n) + 31) & ~31;
+    return c;
+}
+constexpr int kCombineGrid = 1024;
+
+struct ChunkSpace {
+    float* tmp_stats;     // packed statistics of one chunk
+    double* part_ll;      // [kCombineGrid][2] partial (sum ll, sum g) of the combine kernel
+    int* nonpd_acc;       // non-PD pairs over all chunk launches
+    size_t inner_off;     // the single-chunk workspace starts here
+    size_t bytes;
+};
+ChunkSpace chunk_space(void* base, int D, int Kc, size_t inner_bytes) {
+    ChunkSpace c;
+    char* b = (char*)base;
+    size_t off = 0;
+    c.tmp_stats = (float*)(b + off); off += up256((size_t)dgmm_stats_len(D, Kc) * 4);
+    c.part_ll = (double*)(b + off);  off += up256((size_t)kCombineGrid * 2 * 8);
+    c.nonpd_acc = (int*)(b + off);   off += 256;
+    c.inner_off = off;
+    c.bytes = off + inner_bytes;
+    return c;
+}
+
+__global__ void nonpd_accum_kernel(const int* __restrict__ nonpd, int* __restrict__ acc, int reset) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *acc = (reset ? 0 : *acc) + (nonpd ? *nonpd : 0);
+}
+
+// llc [n][N]: in = chunk log-likelihoods, out = chunk weights g_i exp(ll_c - ll_i) (when want_w).
+__global__ void __launch_bounds__(256) chunk_combine_kernel(float* __restrict__ llc, int n, long long N,
+                                                            const float* __restrict__ g, float* __restrict__ out_ll,
+                                                            int want_w, double* __restrict__ part) {
+    __shared__ double sh[2][8];
+    double ll_acc = 0.0, g_acc = 0.0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long long)gridDim.x * blockDim.x) {
+        float m = -INFINITY;
+        bool nan = false;
+        for (int c = 0; c < n; ++c) {
+            const float v = llc[(size_t)c * N + i];
+            nan = nan || !(v == v);
+            m = fmaxf(m, v);
+        }
+        float ll;
+        if (nan) {
+            ll = -INFINITY;
+        } else if (m == -INFINITY) {
+            ll = -INFINITY;
+        } else {
+            float s = 0.f;
+            for (int c = 0; c < n; ++c) s += expf(llc[(size_t)c * N + i] - m);
+            ll = m + logf(s);
+        }
+        const float gi = g ? g[i] : 1.f;
+        if (want_w) {
+            for (int c = 0; c < n; ++c) {
+                const float v = llc[(size_t)c * N + i];
+                llc[(size_t)c * N + i] = (ll > -INFINITY) ? gi * expf(v - ll) : 0.f;
+            }
+        }
+        if (out_ll) out_ll[i] = ll;
+        ll_acc += (double)ll;
+        g_acc += (double)gi;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ll_acc += __shfl_xor_sync(0xffffffffu, ll_acc, o);
+        g_acc += __shfl_xor_sync(0xffffffffu, g_acc, o);
+    }
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = ll_acc; sh[1][threadIdx.x >> 5] = g_acc; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int w = 0; w < 8; ++w) { a += sh[0][w]; b += sh[1][w]; }
+        part[2 * blockIdx.x] = a;
+        part[2 * blockIdx.x + 1] = b;
+    }
+}
+
+// Chunk statistics (packed for Kc components) -> components [c0, c0 + Kc) of the caller's packed buffer.
+__global__ void scatter_stats_kernel(const float* __restrict__ tmp, int Kc, int c0, int K, int D, float* __restrict__ out,
+                                     int beta) {
+    const int per = 1 + D + D * D;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < Kc * per; idx += gridDim.x * blockDim.x) {
+        int src, dst;
+        if (idx < Kc) {
+            src = idx; dst = c0 + idx;
+        } else if (idx < Kc + Kc * D) {
+            const int r = idx - Kc;
+            src = idx; dst = K + c0 * D + r;
+        } else {
+            const int r = idx - Kc - Kc * D;
+            src = idx; dst = K + K * D + c0 * D * D + r;
+        }
+        out[dst] = beta ? out[dst] + tmp[src] : tmp[src];
+    }
+}
+
+// Tail of the packed buffer from the combine kernel's partial sums (fixed order: deterministic).
+__global__ void chunk_tail_kernel(const double* __restrict__ part, int nblk, const int* __restrict__ nonpd_acc,
+                                  float* __restrict__ tail, int beta) {
+    double ll = 0.0, sg = 0.0;
+    for (int b = threadIdx.x; b < nblk; b += 32) { ll += part[2 * b]; sg += part[2 * b + 1]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ll += __shfl_xor_sync(0xffffffffu, ll, o);
+        sg += __shfl_xor_sync(0xffffffffu, sg, o);
+    }
+    if (threadIdx.x == 0) {
+        if (beta) ll += (double)tail[0] + (double)tail[1];
+        const float hi = (float)ll;
+        tail[0] = hi;
+        tail[1] = isfinite(hi) ? (float)(ll - (double)hi) : 0.f;
+        tail[2] = beta ? tail[2] + (float)sg : (float)sg;
+        tail[3] = beta ? tail[3] + (float)(*nonpd_acc) : (float)(*nonpd_acc);
+    }
+}
+
+// Chunked log-likelihood pass: fills llc [n][N] (chunk values, or chunk weights when want_w), out_ll (optional),
+// the combine partials and the non-PD accumulator.
+int chunked_loglik(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+                   const float* mu, const float* Sigma, const float* g, float* out_ll, int want_w, float* llc,
+                   const ChunkSpace& cs, void* inner_ws, size_t inner_bytes, cudaStream_t st, int* nblk) {
+    const KChunks kc = k_chunks(K);
+    for (int c = 0; c < kc.n; ++c) {
+        const int c0 = c * kc.Kc, k = std::min(kc.Kc, K - c0);
+        Workspace ws;
+        int nb = 0;
+        int rc = loglik_pass_1(X, S, noise, N, D, k, log_alpha + c0, mu + (size_t)c0 * D, Sigma + (size_t)c0 * D * D,
+                               llc + (size_t)c * N, inner_ws, inner_bytes, st, &ws, &nb);
+        if (rc) return rc;
+        nonpd_accum_kernel<<<1, 32, 0, st>>>(ws.nonpd, cs.nonpd_acc, c == 0);
+        CUDA_TRY(cudaGetLastError());
+    }
+    const int grid = (int)std::min<long long>(kCombineGrid, std::max<long long>(1, (N + 255) / 256));
+    chunk_combine_kernel<<<grid, 256, 0, st>>>(llc, kc.n, N, g, out_ll, want_w, cs.part_ll);
+    CUDA_TRY(cudaGetLastError());
+    *nblk = grid;
+    return 0;
+}
+
+int loglik_pass(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+                const float* mu, const float* Sigma, float* out_ll, void* workspace, size_t workspace_bytes,
+                cudaStream_t st, Workspace* ws_out, int* nblk) {
+    if (K <= kChunkK)
+        return loglik_pass_1(X, S, noise, N, D, K, log_alpha, mu, Sigma, out_ll, workspace, workspace_bytes, st, ws_out, nblk);
+    DeviceInfo dev;
+    int rc = device_info(&dev);
+    if (rc) return rc;
+    if (!workspace) return DGMM_ERR_WORKSPACE;
+    const KChunks kc = k_chunks(K);
+    const size_t inner_bytes = carve(nullptr, D, kc.Kc, dev.sms).bytes;
+    const ChunkSpace cs = chunk_space(workspace, D, kc.Kc, inner_bytes);
+    if (cs.bytes > workspace_bytes) return DGMM_ERR_WORKSPACE;
+    float* llc = nullptr;
+    CUDA_TRY(cudaMallocAsync((void**)&llc, (size_t)kc.n * std::max<int64_t>(N, 1) * 4, st));
+    rc = chunked_loglik(X, S, noise, N, D, K, log_alpha, mu, Sigma, nullptr, out_ll, 0, llc, cs,
+                        (char*)workspace + cs.inner_off, inner_bytes, st, nblk);
+    cudaFreeAsync(llc, st);
+    if (rc) return rc;
+    // what the callers' finalize_ll_kernel reads: per-block (sum ll) partials and the non-PD count
+    Workspace ws = carve((char*)workspace + cs.inner_off, D, kc.Kc, dev.sms);
+    ws.part_ll = cs.part_ll;
+    ws.nonpd = cs.nonpd_acc;
+    *ws_out = ws;
+    return 0;
+}
+
+int stats_pass(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
+               const float* mu, const float* Sigma, const float* g, float resp_floor, float* out_ll, float* out_stats,
+               int beta, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+    if (K <= kChunkK)
+        return stats_pass_1(X, S, noise, N, D, K, log_alpha, mu, Sigma, g, resp_floor, out_ll, out_stats, beta, workspace,
+                            workspace_bytes, st);
+    DeviceInfo dev;
+    int rc = device_info(&dev);
+    if (rc) return rc;
+    if (!workspace) return DGMM_ERR_WORKSPACE;
+    const KChunks kc = k_chunks(K);
+    const size_t inner_bytes = carve(nullptr, D, kc.Kc, dev.sms).bytes;
+    const ChunkSpace cs = chunk_space(workspace, D, kc.Kc, inner_bytes);
+    if (cs.bytes > workspace_bytes) return DGMM_ERR_WORKSPACE;
+    void* inner_ws = (char*)workspace + cs.inner_off;
+    const int64_t Np = std::max<int64_t>(N, 1);
+    float* llc = nullptr;
+    CUDA_TRY(cudaMallocAsync((void**)&llc, (size_t)(kc.n + 1) * Np * 4, st));
+    float* ll_scratch = llc + (size_t)kc.n * Np;      // ll carrier of the cooperative path (D > 16)
+    int nblk = 0;
+    rc = chunked_loglik(X, S, noise, N, D, K, log_alpha, mu, Sigma, g, out_ll, 1, llc, cs, inner_ws, inner_bytes, st, &nblk);
+    for (int c = 0; c < kc.n && rc == 0; ++c) {
+        const int c0 = c * kc.Kc, k = std::min(kc.Kc, K - c0);
+        rc = stats_pass_1(X, S, noise, N, D, k, log_alpha + c0, mu + (size_t)c0 * D, Sigma + (size_t)c0 * D * D,
+                          llc + (size_t)c * Np, resp_floor, ll_scratch, cs.tmp_stats, 0, inner_ws, inner_bytes, st);
+        if (rc) break;
+        scatter_stats_kernel<<<64, 256, 0, st>>>(cs.tmp_stats, k, c0, K, D, out_stats, beta);
+        if (cudaGetLastError() != cudaSuccess) rc = DGMM_ERR_BAD_ARG;
+    }
+    cudaFreeAsync(llc, st);
+    if (rc) return rc;
+    chunk_tail_kernel<<<1, 32, 0, st>>>(cs.part_ll, nblk, cs.nonpd_acc, out_stats + (size_t)K * (1 + D + D * D), beta);
+    return (int)cudaGetLastError();
+}
+
 }  // namespace
 
 // =======================================================================================
@@ -972,11 +1199,16 @@ size_t dgmm_workspace_bytes(int D, int K) {
     if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return 0;
     DeviceInfo dev;
     if (device_info(&dev)) return 0;
+    if (K > kChunkK) {
+        const KChunks kc = k_chunks(K);
+        return chunk_space(nullptr, D, kc.Kc, carve(nullptr, D, kc.Kc, dev.sms).bytes).bytes;
+    }
     return carve(nullptr, D, K, dev.sms).bytes;
 }
 
 int dgmm_stats_needs_ll(int D, int K, int noise_layout) {
     if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return 0;
+    if (K > kChunkK) return 0;    // the chunked path carries ll_i in its own scratch
     return use_team_path(D, K, MODE_STATS, noise_layout) ? 1 : 0;
 }
 
@@ -1015,6 +1247,7 @@ int dgmm_debug_get_plan(int mode, int D, int K, int64_t N, int noise, int has_g,
     int rc = device_info(&dev);
     if (rc) return rc;
     if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return DGMM_ERR_BAD_ARG;
+    if (K > kChunkK) K = k_chunks(K).Kc;      // component chunks: the plan of one chunk launch
     if (use_team_path(D, K, mode, noise)) {
         // cooperative path: sigp = 3 marks it; GS = teams per block, NSLOT = component chunks
         TeamPlan t;
@@ -1079,8 +1312,8 @@ int dgmm_estep_full_f32(const float* X, const float* S, int noise_layout, int64_
         f.out_log_r = out_log_r; f.out_b = out_b; f.out_B = out_B; f.nonpd = ws.nonpd;
         f.N = N; f.K = K; f.noise = noise_layout;
         const void* k = kDims[D].full();
-        const long long pairs = (long long)N * K;
-        const long long blocks = (pairs + 127) / 128;
+        // one block per (tile of 128 points, component)
+        const long long blocks = ((long long)N + 127) / 128 * K;
         if (blocks > 0x7fffffffLL) return DGMM_ERR_BAD_ARG;
         void* args[] = {&f};
         CUDA_TRY(cudaLaunchKernel(k, dim3((unsigned)blocks), dim3(128), args, 0, st));
@@ -1212,9 +1445,68 @@ struct dgmm_ctx {
     float* h_tail;   // pinned, 4 floats
     void* ws;
     size_t ws_bytes;
+    // resident table (dgmm_ctx_upload)
+    float* rX;
+    float* rS;
+    float* r_ll;
+    int64_t rN;
+    int r_layout;
 };
 
+// S_full [N,D,D] -> packed lower triangles [N,ND]
+__global__ void pack_noise_kernel(const float* __restrict__ S, long long N, int D, float* __restrict__ out) {
+    const int ND = D * (D + 1) / 2;
+    const long long total = N * ND;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        const long long i = idx / ND;
+        const int e = (int)(idx - i * ND);
+        int a = 0;
+        while ((a + 1) * (a + 2) / 2 <= e) ++a;
+        const int b = e - a * (a + 1) / 2;
+        out[idx] = S[(size_t)i * D * D + a * D + b];
+    }
+}
+
 extern "C" {
+
+int dgmm_pack_noise_f32(const float* S_full, int64_t N, int D, float* S_packed, void* stream) {
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (N < 0 || (N > 0 && (!S_full || !S_packed))) return DGMM_ERR_BAD_ARG;
+    if (N == 0) return 0;
+    const long long total = (long long)N * (D * (D + 1) / 2);
+    const int grid = (int)std::min<long long>((total + 255) / 256, 148 * 16);
+    pack_noise_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(S_full, (long long)N, D, S_packed);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// Host packer: row a of the lower triangle is a + 1 contiguous floats in both layouts (one memcpy per row);
+// the points are split over the host threads.
+int dgmm_pack_noise_host(const float* S_full, int64_t N, int D, float* S_packed) {
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (N < 0 || (N > 0 && (!S_full || !S_packed))) return DGMM_ERR_BAD_ARG;
+    const int ND = D * (D + 1) / 2;
+    auto work = [=](int64_t lo, int64_t hi) {
+        for (int64_t i = lo; i < hi; ++i) {
+            const float* src = S_full + (size_t)i * D * D;
+            float* dst = S_packed + (size_t)i * ND;
+            for (int a = 0; a < D; ++a) memcpy(dst + a * (a + 1) / 2, src + a * D, (size_t)(a + 1) * 4);
+        }
+    };
+    unsigned nt = std::thread::hardware_concurrency();
+    if (nt < 1) nt = 1;
+    if (nt > 32) nt = 32;
+    if (N < 65536 || nt == 1) { work(0, N); return 0; }
+    std::vector<std::thread> th;
+    const int64_t per = (N + nt - 1) / nt;
+    for (unsigned t = 0; t < nt; ++t) {
+        const int64_t lo = (int64_t)t * per, hi = std::min<int64_t>(N, lo + per);
+        if (lo < hi) th.emplace_back(work, lo, hi);
+    }
+    for (auto& t : th) t.join();
+    return 0;
+}
 
 int dgmm_ctx_create(dgmm_ctx** out, int device, int D, int K, int64_t chunk_points) {
     if (!out || chunk_points < 1) return DGMM_ERR_BAD_ARG;
@@ -1261,6 +1553,9 @@ void dgmm_ctx_destroy(dgmm_ctx* c) {
     }
     cudaFree(c->d_alpha); cudaFree(c->d_log_alpha); cudaFree(c->d_mu); cudaFree(c->d_Sigma);
     cudaFree(c->d_stats); cudaFree(c->d_sum); cudaFree(c->ws);
+    if (c->rX) cudaFree(c->rX);
+    if (c->rS) cudaFree(c->rS);
+    if (c->r_ll) cudaFree(c->r_ll);
     cudaFreeHost(c->h_sum); cudaFreeHost(c->h_tail);
     if (c->copy_st) cudaStreamDestroy(c->copy_st);
     if (c->comp_st) cudaStreamDestroy(c->comp_st);
@@ -1270,7 +1565,8 @@ void dgmm_ctx_destroy(dgmm_ctx* c) {
 }  // extern "C"
 
 static size_t noise_floats(int D, int layout) {
-    return layout == DGMM_NOISE_FULL ? (size_t)D * D : (layout == DGMM_NOISE_DIAG ? (size_t)D : 0);
+    return layout == DGMM_NOISE_FULL ? (size_t)D * D
+           : (layout == DGMM_NOISE_DIAG ? (size_t)D : (layout == DGMM_NOISE_PACKED ? (size_t)D * (D + 1) / 2 : 0));
 }
 
 // Streams the chunks of (X, S) through the two device buffers: copy stream uploads chunk c+1
@@ -1334,7 +1630,7 @@ static int stats_pass_host(dgmm_ctx* c, const float* X, const float* S, int layo
 int dgmm_estep_stats_host(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, const float* alpha,
                           const float* mu, const float* Sigma, float resp_floor, float* out_stats) {
     if (!c || !alpha || !mu || !Sigma || !out_stats) return DGMM_ERR_BAD_ARG;
-    if (layout < 0 || layout > 3) return DGMM_ERR_LAYOUT;
+    if (layout < 0 || layout > 4) return DGMM_ERR_LAYOUT;
     if (layout == DGMM_NOISE_SHARED && c->chunk < c->D) return DGMM_ERR_BAD_ARG;
     CUDA_TRY(cudaSetDevice(c->device));
     int rc = upload_params(c, alpha, mu, Sigma);
@@ -1350,7 +1646,7 @@ int dgmm_estep_stats_host(dgmm_ctx* c, const float* X, const float* S, int layou
 int dgmm_em_iteration_host(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, float w, float* alpha,
                            float* mu, float* Sigma, double* ll_sum, int64_t* nonpd) {
     if (!c || !alpha || !mu || !Sigma) return DGMM_ERR_BAD_ARG;
-    if (layout < 0 || layout > 3) return DGMM_ERR_LAYOUT;
+    if (layout < 0 || layout > 4) return DGMM_ERR_LAYOUT;
     if (layout == DGMM_NOISE_SHARED && c->chunk < c->D) return DGMM_ERR_BAD_ARG;
     CUDA_TRY(cudaSetDevice(c->device));
     const int D = c->D, K = c->K;
@@ -1378,7 +1674,7 @@ int dgmm_em_iteration_host(dgmm_ctx* c, const float* X, const float* S, int layo
 int dgmm_score_host(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, const float* alpha,
                     const float* mu, const float* Sigma, float* out_ll, double* ll_sum, int64_t* nonpd) {
     if (!c || !alpha || !mu || !Sigma) return DGMM_ERR_BAD_ARG;
-    if (layout < 0 || layout > 3) return DGMM_ERR_LAYOUT;
+    if (layout < 0 || layout > 4) return DGMM_ERR_LAYOUT;
     CUDA_TRY(cudaSetDevice(c->device));
     const int D = c->D, K = c->K;
     cudaStream_t st = c->comp_st;
@@ -1402,6 +1698,121 @@ int dgmm_score_host(dgmm_ctx* c, const float* X, const float* S, int layout, int
     const double total = c->h_sum[0];
     const int64_t bad = (int64_t)c->h_sum[1];
     if (ll_sum) *ll_sum = bad ? -INFINITY : total;
+    if (nonpd) *nonpd = bad;
+    return 0;
+}
+
+// ---- resident table -------------------------------------------------------------------------
+int dgmm_ctx_upload(dgmm_ctx* c, const float* X, const float* S, int layout, int64_t N, int pack_full) {
+    if (!c || N < 0 || (N > 0 && !X)) return DGMM_ERR_BAD_ARG;
+    if (layout < 0 || layout > 4) return DGMM_ERR_LAYOUT;
+    if (N > 0 && layout != DGMM_NOISE_NONE && !S) return DGMM_ERR_BAD_ARG;
+    CUDA_TRY(cudaSetDevice(c->device));
+    const int D = c->D;
+    CUDA_TRY(cudaStreamSynchronize(c->comp_st));
+    if (c->rX) { cudaFree(c->rX); c->rX = nullptr; }
+    if (c->rS) { cudaFree(c->rS); c->rS = nullptr; }
+    if (c->r_ll) { cudaFree(c->r_ll); c->r_ll = nullptr; }
+    const bool pack = pack_full && layout == DGMM_NOISE_FULL;
+    const int res_layout = pack ? DGMM_NOISE_PACKED : layout;
+    const size_t nf_res = layout == DGMM_NOISE_SHARED ? 0 : noise_floats(D, res_layout);
+    const int64_t Np = std::max<int64_t>(N, 1);
+    CUDA_TRY(cudaMalloc(&c->rX, (size_t)Np * D * 4));
+    CUDA_TRY(cudaMalloc(&c->r_ll, (size_t)Np * 4));
+    if (layout == DGMM_NOISE_SHARED) {
+        CUDA_TRY(cudaMalloc(&c->rS, (size_t)D * D * 4));
+        CUDA_TRY(cudaMemcpyAsync(c->rS, S, (size_t)D * D * 4, cudaMemcpyHostToDevice, c->comp_st));
+    } else if (nf_res) {
+        CUDA_TRY(cudaMalloc(&c->rS, (size_t)Np * nf_res * 4));
+    }
+    c->rN = N;
+    c->r_layout = res_layout;
+    if (N == 0) return 0;
+    if (!pack) {
+        CUDA_TRY(cudaMemcpyAsync(c->rX, X, (size_t)N * D * 4, cudaMemcpyHostToDevice, c->comp_st));
+        if (nf_res) CUDA_TRY(cudaMemcpyAsync(c->rS, S, (size_t)N * nf_res * 4, cudaMemcpyHostToDevice, c->comp_st));
+    } else {
+        // full matrices stream through the chunk buffers and are packed on the device as they arrive
+        int rc = stream_chunks(c, X, S, layout, N, [&](int, int64_t off, int64_t n, const float* dX, const float* dS) -> int {
+            CUDA_TRY(cudaMemcpyAsync(c->rX + (size_t)off * D, dX, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, c->comp_st));
+            return dgmm_pack_noise_f32(dS, n, D, c->rS + (size_t)off * nf_res, c->comp_st);
+        });
+        if (rc) return rc;
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->comp_st));
+    return 0;
+}
+
+static int resident_stats(dgmm_ctx* c, float resp_floor) {
+    return stats_pass(c->rX, c->rS, c->r_layout, c->rN, c->D, c->K, c->d_log_alpha, c->d_mu, c->d_Sigma, nullptr,
+                      resp_floor, c->r_ll, c->d_stats, 0, c->ws, c->ws_bytes, c->comp_st);
+}
+
+int dgmm_em_fit_resident(dgmm_ctx* c, int max_iters, float w, double tol, float* alpha, float* mu, float* Sigma,
+                         int* iters_done, double* ll_trace, int64_t* nonpd) {
+    if (!c || !alpha || !mu || !Sigma || max_iters < 0 || !c->rX) return DGMM_ERR_BAD_ARG;
+    CUDA_TRY(cudaSetDevice(c->device));
+    const int D = c->D, K = c->K;
+    cudaStream_t st = c->comp_st;
+    int rc = upload_params(c, alpha, mu, Sigma);
+    if (rc) return rc;
+    double prev = -INFINITY;
+    int done = 0;
+    int64_t bad_total = 0;
+    for (int it = 0; it < max_iters; ++it) {
+        rc = resident_stats(c, 0.f);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpyAsync(c->h_tail, c->d_stats + (size_t)K * (1 + D + D * D), 4 * sizeof(float),
+                                 cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));                       // the one host sync of the iteration (base.py:48)
+        const bool bad = c->h_tail[3] > 0.f;
+        const double ll = bad ? -INFINITY : (double)c->h_tail[0] + (double)c->h_tail[1];
+        if (ll_trace) ll_trace[it] = ll;
+        bad_total = (int64_t)c->h_tail[3];
+        if (bad || ll != ll) break;                                // base.py:48-49: parameters stay as they were
+        rc = dgmm_mstep_update_f32(c->d_stats, (double)c->rN, w, D, K, c->d_mu, c->d_Sigma, c->d_alpha, c->d_log_alpha, st);
+        if (rc) return rc;
+        ++done;
+        if (fabs(ll - prev) < tol) break;                          // base.py:52-53
+        prev = ll;
+    }
+    if (iters_done) *iters_done = done;
+    if (nonpd) *nonpd = bad_total;
+    CUDA_TRY(cudaMemcpyAsync(alpha, c->d_alpha, (size_t)K * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(mu, c->d_mu, (size_t)K * D * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(Sigma, c->d_Sigma, (size_t)K * D * D * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int dgmm_em_iteration_resident(dgmm_ctx* c, float w, float* alpha, float* mu, float* Sigma, double* ll_sum,
+                               int64_t* nonpd) {
+    int done = 0;
+    double ll = -INFINITY;
+    const int rc = dgmm_em_fit_resident(c, 1, w, -1.0, alpha, mu, Sigma, &done, &ll, nonpd);
+    if (rc) return rc;
+    if (ll_sum) *ll_sum = ll;
+    return 0;
+}
+
+int dgmm_score_resident(dgmm_ctx* c, const float* alpha, const float* mu, const float* Sigma, float* out_ll,
+                        double* ll_sum, int64_t* nonpd) {
+    if (!c || !alpha || !mu || !Sigma || !c->rX) return DGMM_ERR_BAD_ARG;
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = c->comp_st;
+    { int rcp = upload_params(c, alpha, mu, Sigma); if (rcp) return rcp; }
+    Workspace ws;
+    int nblk = 0;
+    int rc = loglik_pass(c->rX, c->rS, c->r_layout, c->rN, c->D, c->K, c->d_log_alpha, c->d_mu, c->d_Sigma, c->r_ll, c->ws,
+                         c->ws_bytes, st, &ws, &nblk);
+    if (rc) return rc;
+    finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, nblk, c->d_sum, nullptr, 0);
+    CUDA_TRY(cudaGetLastError());
+    if (out_ll && c->rN > 0) CUDA_TRY(cudaMemcpyAsync(out_ll, c->r_ll, (size_t)c->rN * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_sum, c->d_sum, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const int64_t bad = (int64_t)c->h_sum[1];
+    if (ll_sum) *ll_sum = bad ? -INFINITY : c->h_sum[0];
     if (nonpd) *nonpd = bad;
     return 0;
 }

@@ -47,6 +47,9 @@ struct SampleParams {
 
 }  // namespace dgmm
 
+// the loop over the rows of B_ij: fully unrolled with the rest (compile-time row offsets and divisors in the
+// staged stores) for D <= 16, rolled above
+#define DGMM_FULL_CLOOP _Pragma("unroll")
 #define DGMM_LOOP _Pragma("unroll")
 namespace dgmm {
 namespace unrolled {
@@ -54,7 +57,9 @@ namespace unrolled {
 }  // namespace unrolled
 }  // namespace dgmm
 #undef DGMM_LOOP
+#undef DGMM_FULL_CLOOP
 
+#define DGMM_FULL_CLOOP _Pragma("unroll 1")
 #define DGMM_LOOP _Pragma("unroll 4")
 namespace dgmm {
 namespace rolled {
@@ -62,3 +67,4 @@ namespace rolled {
 }  // namespace rolled
 }  // namespace dgmm
 #undef DGMM_LOOP
+#undef DGMM_FULL_CLOOP

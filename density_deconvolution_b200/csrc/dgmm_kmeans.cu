@@ -330,9 +330,11 @@ int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, const float*
 int dgmm_gather_points_f32(const float* X, const float* S, int noise_layout, const int64_t* idx, int64_t B, int D,
                            float* outX, float* outS, void* stream) {
     if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
-    if (noise_layout != DGMM_NOISE_FULL && noise_layout != DGMM_NOISE_DIAG && noise_layout != DGMM_NOISE_NONE)
+    if (noise_layout != DGMM_NOISE_FULL && noise_layout != DGMM_NOISE_DIAG && noise_layout != DGMM_NOISE_NONE &&
+        noise_layout != DGMM_NOISE_PACKED)
         return DGMM_ERR_LAYOUT;
-    const int n_s = noise_layout == DGMM_NOISE_FULL ? D * D : (noise_layout == DGMM_NOISE_DIAG ? D : 0);
+    const int n_s = noise_layout == DGMM_NOISE_FULL ? D * D
+                    : (noise_layout == DGMM_NOISE_DIAG ? D : (noise_layout == DGMM_NOISE_PACKED ? D * (D + 1) / 2 : 0));
     if (B < 0 || (B > 0 && (!X || !idx || !outX || (n_s && (!S || !outS))))) return DGMM_ERR_BAD_ARG;
     if (B == 0) return 0;
     int sms = 0, optin = 0;

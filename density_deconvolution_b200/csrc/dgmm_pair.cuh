@@ -34,8 +34,12 @@
 namespace dgmm {
 
 enum : int { MODE_LOGLIK = 0, MODE_STATS = 1 };
+// Largest D whose log-likelihood kernel re-forms the next point's T inside the factorisation (refill).
+#ifndef DGMM_LL_ROTATE_D
+#define DGMM_LL_ROTATE_D 12
+#endif
 enum : int { ST_REG = 0, ST_SMEM = 1, ST_GLOBAL = 2, ST_TMEM = 3 };  // where Sigma_j / accumulators live
-enum : int { NOISE_FULL = 0, NOISE_DIAG = 1, NOISE_NONE = 2, NOISE_SHARED = 3 };
+enum : int { NOISE_FULL = 0, NOISE_DIAG = 1, NOISE_NONE = 2, NOISE_SHARED = 3, NOISE_PACKED = 4 };
 
 constexpr int kMaxStages = 4;
 constexpr int kPairMaxThreads = 256;  // largest block the pair kernel is compiled for
@@ -43,7 +47,7 @@ constexpr int kSmemHeader = 1152;  // mbarriers (64 B) + logsumexp exchange (2 x
 
 struct PairParams {
     const float* X;          // [N,D]
-    const float* S;          // [N,D,D] | [N,D] | unused
+    const float* S;          // [N,D,D] | [N,D] | [N,D(D+1)/2] (packed lower triangles) | unused
     const float* g;          // [N] or null
     const float* sig_cols;   // [ND][GS]  transposed packed lower triangles (+ shared noise folded in)
     const float* mu_cols;    // [D][GS]
@@ -58,7 +62,7 @@ struct PairParams {
     int use_bulk;
     float resp_floor;
     // derived on the host (constant-bank operands in the kernel): ring-stage layout and loop counts
-    int n_s;          // noise floats per point in the tile (D*D | D | 0)
+    int n_s;          // noise floats per point in the tile (D*D | D | D(D+1)/2 | 0)
     int off_X, off_g; // byte offsets of the X and g sub-tiles inside a stage (S sits at 0)
     int stage_bytes;
     int rounds;       // PT / NSLOT
@@ -163,7 +167,7 @@ __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.
 // group classes of the pair kernel (see dgmm_pair_body.inc)
 enum : int { GCLS_SUB = 0, GCLS_WARP = 1, GCLS_MW4 = 2, GCLS_MWN = 3, GCLS_ANY = 4 };
 // noise classes of the pair kernel
-enum : int { NZ_FULL = 0, NZ_DIAG = 1, NZ_ANY = 2 };
+enum : int { NZ_FULL = 0, NZ_DIAG = 1, NZ_ANY = 2, NZ_PACKED = 3 };
 
 // predicated 32-bit global store (no branch in the instruction stream)
 __device__ __forceinline__ void st_global_if(float* ptr, float v, bool pred) {
@@ -193,15 +197,21 @@ __host__ __device__ inline int lse_lanes(int TPB, int PT) {
     return r;
 }
 
-// Full per-point noise with odd D: the pair kernel re-packs the tile's lower triangles into 16-byte
-// aligned rows (compiled placements with a fixed noise class only).
+// The pair kernel re-packs a tile's noise into 16-byte aligned rows (128-bit shared-memory reads) where the
+// input layout does not give them (compiled placements with a fixed noise class only):
+//   full noise with odd D          -> lower triangles as rows of RS = roundup4(D) floats, [PT][D][RS]
+//   packed noise with ND % 4 != 0  -> packed triangles at a stride of roundup4(ND) floats, [PT][NDp]
 __host__ __device__ constexpr bool repack_noise(int D, int nz) {
-    return nz == NZ_FULL && (D & 1) && D > 1 && D <= DGMM_UNROLL_D;
+    return (nz == NZ_FULL && (D & 1) && D > 1 && D <= DGMM_UNROLL_D) ||
+           (nz == NZ_PACKED && ((D * (D + 1) / 2) & 3) != 0 && D <= DGMM_UNROLL_D);
+}
+__host__ __device__ constexpr int repack_floats_per_point(int D, int nz) {
+    return !repack_noise(D, nz) ? 0 : (nz == NZ_PACKED ? ((D * (D + 1) / 2 + 3) & ~3) : D * ((D + 3) & ~3));
 }
 
 // Bytes of one ring stage and the offsets of its three sub-tiles (all multiples of 16).
 __host__ __device__ inline int noise_floats_per_point(int D, int noise) {
-    return noise == NOISE_FULL ? D * D : (noise == NOISE_DIAG ? D : 0);
+    return noise == NOISE_FULL ? D * D : (noise == NOISE_DIAG ? D : (noise == NOISE_PACKED ? D * (D + 1) / 2 : 0));
 }
 __host__ __device__ inline int align16(int b) { return (b + 15) & ~15; }
 struct StageLayout {

@@ -104,18 +104,19 @@ __global__ void sgd_component_kernel(int update, const float* __restrict__ stats
     Sigma[(size_t)j * D * D + t] = s;
 }
 
-// One block of 256 threads (K <= 256).  update == 0: only log_alpha = log_softmax(soft_weights).
+// One block of roundup(K) threads: 256, 512 or 1024 (K <= 1024).  update == 0: only log_alpha = log_softmax(soft_weights).
 // epoch_acc (optional, 2 doubles): += (sum_i ll_i of the minibatch, non-PD pair count) from the stats tail.
 __global__ void sgd_weights_kernel(int update, const float* __restrict__ stats, float inv_n, AdamCfg cfg, int D, int K,
                                    float* __restrict__ soft_weights, float* m_sw, float* v_sw,
                                    float* __restrict__ log_alpha, double* epoch_acc) {
-    __shared__ float red[256];
-    __shared__ float red2[256];
+    __shared__ float red[1024];
+    __shared__ float red2[1024];
     const int t = threadIdx.x;
+    const int half = blockDim.x >> 1;
     auto block_max = [&](float v) {
         red[t] = v;
         __syncthreads();
-        for (int o = 128; o > 0; o >>= 1) {
+        for (int o = half; o > 0; o >>= 1) {
             if (t < o) red[t] = fmaxf(red[t], red[t + o]);
             __syncthreads();
         }
@@ -127,7 +128,7 @@ __global__ void sgd_weights_kernel(int update, const float* __restrict__ stats, 
         red[t] = v;
         red2[t] = w;
         __syncthreads();
-        for (int o = 128; o > 0; o >>= 1) {
+        for (int o = half; o > 0; o >>= 1) {
             if (t < o) { red[t] += red[t + o]; red2[t] += red2[t + o]; }
             __syncthreads();
         }
@@ -161,6 +162,8 @@ __global__ void sgd_weights_kernel(int update, const float* __restrict__ stats, 
     if (t < K) log_alpha[t] = (w - mx) - logf(se);
 }
 
+inline int weights_block(int K) { return K <= 256 ? 256 : (K <= 512 ? 512 : 1024); }
+
 int check_shape(int D, int K) {
     if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
     if (K < 1 || K > DGMM_MAX_K) return DGMM_ERR_UNSUPPORTED_K;
@@ -182,7 +185,7 @@ int dgmm_sgd_params_f32(const float* soft_weights, const float* l_diag, const fl
         0, nullptr, 0.f, 0.f, cfg, D, K, nullptr, const_cast<float*>(l_diag), const_cast<float*>(l_lower), nullptr,
         nullptr, nullptr, nullptr, nullptr, nullptr, Sigma);
     CUDA_TRY(cudaGetLastError());
-    sgd_weights_kernel<<<1, 256, 0, st>>>(0, nullptr, 0.f, cfg, D, K, const_cast<float*>(soft_weights), nullptr, nullptr,
+    sgd_weights_kernel<<<1, weights_block(K), 0, st>>>(0, nullptr, 0.f, cfg, D, K, const_cast<float*>(soft_weights), nullptr, nullptr,
                                           log_alpha, nullptr);
     CUDA_TRY(cudaGetLastError());
     return 0;
@@ -211,9 +214,55 @@ int dgmm_sgd_adam_step_f32(const float* stats, double n_batch, double n_total, f
                                                                       l_lower, exp_avg[1], exp_avg_sq[1], exp_avg[2],
                                                                       exp_avg_sq[2], exp_avg[3], exp_avg_sq[3], Sigma);
     CUDA_TRY(cudaGetLastError());
-    sgd_weights_kernel<<<1, 256, 0, st>>>(1, stats, inv_n, cfg, D, K, soft_weights, exp_avg[0], exp_avg_sq[0], log_alpha,
+    sgd_weights_kernel<<<1, weights_block(K), 0, st>>>(1, stats, inv_n, cfg, D, K, soft_weights, exp_avg[0], exp_avg_sq[0], log_alpha,
                                           epoch_acc);
     CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// One minibatch step of BaseSGDGMM.fit as ONE call (the host side of a step is otherwise three ctypes round trips
+// plus their Python argument checks, which at D = 10, K = 64 cost as much as the kernels):
+//   phase & 1: gather the rows perm[batch_lo .. batch_lo + B) of the resident table into bufX / bufS (perm == NULL:
+//              the batch is the contiguous slice starting at batch_lo), then the fused statistics pass -> stats
+//   phase & 2: chain rule + Adam + re-parametrisation from stats (dgmm_sgd_adam_step_f32)
+// Single process: phase = 3.  Under torch.distributed: phase 1, all-reduce of `stats` by the caller, phase 2.
+int dgmm_sgd_fused_step_f32(const float* X, const float* S, int noise_layout, int D, int K, const int64_t* perm,
+                            int64_t batch_lo, int64_t B, float* bufX, float* bufS, float* ll_scratch, int phase,
+                            float* stats, double n_batch, double n_total, float w, float lr, float beta1, float beta2,
+                            float eps, int step, float* soft_weights, float* means, float* l_diag, float* l_lower,
+                            float* const* exp_avg, float* const* exp_avg_sq, float* log_alpha, float* Sigma,
+                            double* epoch_acc, void* workspace, size_t workspace_bytes, void* stream) {
+    int rc = check_shape(D, K);
+    if (rc) return rc;
+    if (B < 1 || batch_lo < 0 || !stats) return DGMM_ERR_BAD_ARG;
+    if (phase & 1) {
+        const bool per_point = noise_layout == DGMM_NOISE_FULL || noise_layout == DGMM_NOISE_DIAG ||
+                               noise_layout == DGMM_NOISE_PACKED;
+        const size_t n_s = noise_layout == DGMM_NOISE_FULL ? (size_t)D * D
+                           : (noise_layout == DGMM_NOISE_DIAG ? (size_t)D
+                              : (noise_layout == DGMM_NOISE_PACKED ? (size_t)D * (D + 1) / 2 : 0));
+        const float* bx;
+        const float* bs;
+        if (perm) {
+            if (!bufX || (per_point && !bufS)) return DGMM_ERR_BAD_ARG;
+            rc = dgmm_gather_points_f32(X, per_point ? S : nullptr, per_point ? noise_layout : DGMM_NOISE_NONE,
+                                        perm + batch_lo, B, D, bufX, bufS, stream);
+            if (rc) return rc;
+            bx = bufX;
+            bs = per_point ? bufS : S;
+        } else {
+            bx = X + (size_t)batch_lo * D;
+            bs = per_point ? S + (size_t)batch_lo * n_s : S;
+        }
+        rc = dgmm_estep_stats_f32(bx, bs, noise_layout, B, D, K, log_alpha, means, Sigma, nullptr, 0.f, ll_scratch, stats,
+                                  workspace, workspace_bytes, stream);
+        if (rc) return rc;
+    }
+    if (phase & 2) {
+        rc = dgmm_sgd_adam_step_f32(stats, n_batch, n_total, w, lr, beta1, beta2, eps, step, D, K, soft_weights, means,
+                                    l_diag, l_lower, exp_avg, exp_avg_sq, log_alpha, Sigma, epoch_acc, stream);
+        if (rc) return rc;
+    }
     return 0;
 }
 

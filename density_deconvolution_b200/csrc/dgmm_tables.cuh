@@ -77,6 +77,7 @@ inline PairVariant pair_by_gcls_nz(int gcls) {
 template <int D, int MODE, int SIGP, int ACCP, int MAXT, int MINB>
 inline PairVariant pair_by_gcls(int gcls, int nz) {
     if (nz == NZ_FULL) return pair_by_gcls_nz<D, MODE, SIGP, ACCP, NZ_FULL, MAXT, MINB>(gcls);
+    if (nz == NZ_PACKED) return pair_by_gcls_nz<D, MODE, SIGP, ACCP, NZ_PACKED, MAXT, MINB>(gcls);
     return pair_by_gcls_nz<D, MODE, SIGP, ACCP, NZ_DIAG, MAXT, MINB>(gcls);
 }
 
@@ -102,7 +103,8 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
         }
         return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
     }
-    if (which == 1) {  // alternative placements (tuning sweeps, tools/gpu_ab.sh)
+    if (which == 1) {  // alternative placements (tuning sweeps, tools/gpu_ab.sh); not compiled for packed noise
+        if (nz == NZ_PACKED) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
         if constexpr (D <= 12) {
             if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 4>(gcls, nz);
         } else if constexpr (D > DGMM_UNROLL_D && D <= DGMM_PAIR_UNROLL_D) {

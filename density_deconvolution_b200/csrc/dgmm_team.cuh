@@ -222,7 +222,7 @@ __device__ __forceinline__ TeamSmem team_carve(unsigned char* smem, const TeamPa
     s.tmem_slot = reinterpret_cast<uint32_t*>(smem + 64);
     s.ring = smem + kTeamHeader;
     s.spad = reinterpret_cast<float*>(s.ring + (size_t)p.NST * p.stage_bytes);
-    const bool has_mat = (p.noise == NOISE_FULL || p.noise == NOISE_DIAG);
+    const bool has_mat = (p.noise == NOISE_FULL || p.noise == NOISE_DIAG || p.noise == NOISE_PACKED);
     s.vbuf = s.spad + (has_mat ? p.PT * Geo<D>::ROWS * Geo<D>::RS : 0);
     s.lse = s.vbuf + warps * 2 * kTW * kVS;
     return s;
@@ -277,6 +277,13 @@ __device__ __forceinline__ void team_stage_tile(const TeamParams& p, const TeamS
         for (int idx = tid; idx < p.PT * D; idx += TPB) {
             const int pt = idx / D, a = idx - pt * D;
             sm.spad[(pt * Geo<D>::ROWS + a) * Geo<D>::RS + a] = raw[idx];
+        }
+    } else if (p.noise == NOISE_PACKED) {
+        constexpr int ND = D * (D + 1) / 2;
+        for (int idx = tid; idx < p.PT * ND; idx += TPB) {
+            const int pt = idx / ND, e = idx - pt * ND;
+            const int a = tri_row(e), b = e - tri(a, 0);
+            sm.spad[(pt * Geo<D>::ROWS + a) * Geo<D>::RS + b] = raw[idx];
         }
     }
     __syncthreads();

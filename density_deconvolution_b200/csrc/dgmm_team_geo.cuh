@@ -98,7 +98,7 @@ constexpr int kTeamHeader = 128;   // mbarriers (4 x 8 B), TMEM slot
 __host__ __device__ inline size_t team_smem_bytes(int D, int noise, int PT, int NST, bool has_g, bool stats, int TPB) {
     const TeamStage L = team_stage(D, noise, PT, has_g, stats);
     size_t b = kTeamHeader + (size_t)NST * L.bytes;
-    if (noise == NOISE_FULL || noise == NOISE_DIAG) b += (size_t)PT * geo_rows(D) * geo_rs(D) * 4;  // re-packed noise
+    if (noise == NOISE_FULL || noise == NOISE_DIAG || noise == NOISE_PACKED) b += (size_t)PT * geo_rows(D) * geo_rs(D) * 4;  // re-packed noise
     b += (size_t)(TPB / 32) * 2 * kTW * kVS * 4;                                                     // published vectors
     if (!stats) b += (size_t)PT * kMaxTB * 2 * 4;                                                    // (max, sum) per point and team
     return b;

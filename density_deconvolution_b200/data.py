@@ -76,6 +76,8 @@ class DeviceBatches:
                 self.layout = "shared"
             elif self.S.dim() == 2 and tuple(self.S.shape) == (self.n, D):
                 self.layout = "diag"
+            elif self.S.dim() == 2 and tuple(self.S.shape) == (self.n, D * (D + 1) // 2):
+                self.layout = "packed"
             else:
                 raise ValueError("noise_covars has shape %s; expected [N,D,D], [N,D] or [D,D]" % (tuple(self.S.shape),))
         self.batch_size = int(batch_size) if batch_size else self.n
@@ -85,7 +87,7 @@ class DeviceBatches:
         self.generator = generator
         self.max_batches = None
         # ops.gather_points: X and S rows of a shuffled batch in ONE launch (dgmm_gather_points_f32)
-        self.ops = ops if (ops is not None and self.layout in ("full", "diag")) else None
+        self.ops = ops if (ops is not None and self.layout in ("full", "diag", "packed")) else None
 
     def _own_batches(self):
         if self.drop_last:
@@ -108,7 +110,7 @@ class DeviceBatches:
     def __iter__(self):
         if self.shuffle:
             perm = torch.randperm(self.n, device=self.device, generator=self.generator)
-        per_point = self.layout in ("full", "diag")
+        per_point = self.layout in ("full", "diag", "packed")
         for b in range(len(self)):
             lo = b * self.batch_size
             hi = min(lo + self.batch_size, self.n)

@@ -56,7 +56,9 @@ def _noise_layout(X, S):
         return "shared"
     if S.dim() == 2 and tuple(S.shape) == (N, D):
         return "diag"
-    raise ValueError("noise_covars has shape %s; expected [N,D,D], [N,D] or [D,D]" % (tuple(S.shape),))
+    if S.dim() == 2 and tuple(S.shape) == (N, D * (D + 1) // 2):
+        return "packed"
+    raise ValueError("noise_covars has shape %s; expected [N,D,D], [N,D(D+1)/2], [N,D] or [D,D]" % (tuple(S.shape),))
 
 
 def _global_count(n, device):
@@ -679,15 +681,33 @@ class BaseSGDGMM:
         step = int(states[0]["step"].item())
         log_alpha, Sigma = _ops.sgd_params(data[0], data[2], data[3])
         epoch_acc = torch.zeros(2, dtype=torch.float64, device=self.device)
-        stats = None
-        for b, (X_b, S_b) in enumerate(loader):
-            n = sizes[b]                                                         # global minibatch
-            _, stats = _ops.estep_stats(X_b, S_b, log_alpha, data[1], Sigma, noise=loader.layout,
-                                        want_ll=False, out_stats=stats)
-            _dist.allreduce_stats(stats)
-            step += 1
-            _ops.sgd_adam_step(stats, n, n_total, self.w, group["lr"], group["betas"], group["eps"], step, data,
-                               exp_avg, exp_avg_sq, log_alpha, Sigma, epoch_acc)
+        if hasattr(_ops, "SgdStepper") and loader.X.is_cuda:
+            # one C call per minibatch: gather + statistics (+ all-reduce) + Adam (dgmm_sgd_fused_step_f32)
+            stepper = _ops.SgdStepper(loader.X, loader.S, loader.layout, loader.batch_size, data, exp_avg, exp_avg_sq,
+                                      log_alpha, Sigma, epoch_acc, self.w, group["betas"], group["eps"])
+            perm = torch.randperm(loader.n, device=self.device, generator=loader.generator) if loader.shuffle else None
+            distributed = _dist.is_distributed()
+            bs = loader.batch_size
+            for b in range(len(loader)):
+                lo = b * bs
+                nb = min(bs, loader.n - lo)
+                step += 1
+                if distributed:
+                    stepper.step(perm, lo, nb, 1, sizes[b], n_total, group["lr"], step)
+                    _dist.allreduce_stats(stepper.stats)
+                    stepper.step(perm, lo, nb, 2, sizes[b], n_total, group["lr"], step)
+                else:
+                    stepper.step(perm, lo, nb, 3, sizes[b], n_total, group["lr"], step)
+        else:
+            stats = None
+            for b, (X_b, S_b) in enumerate(loader):
+                n = sizes[b]                                                         # global minibatch
+                _, stats = _ops.estep_stats(X_b, S_b, log_alpha, data[1], Sigma, noise=loader.layout,
+                                            want_ll=False, out_stats=stats)
+                _dist.allreduce_stats(stats)
+                step += 1
+                _ops.sgd_adam_step(stats, n, n_total, self.w, group["lr"], group["betas"], group["eps"], step, data,
+                                   exp_avg, exp_avg_sq, log_alpha, Sigma, epoch_acc)
         for st in states:
             st["step"].fill_(float(step))
         self.optimiser._opt_called = True   # what optimiser.step() records for the lr scheduler's order check

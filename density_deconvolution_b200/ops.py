@@ -65,7 +65,8 @@ def _noise(S, layout, N, D, device):
     if code == _lib.NOISE_NONE:
         return None, code
     S = _f32c(S, "noise_covars", device)
-    want = {_lib.NOISE_FULL: (N, D, D), _lib.NOISE_DIAG: (N, D), _lib.NOISE_SHARED: (D, D)}[code]
+    want = {_lib.NOISE_FULL: (N, D, D), _lib.NOISE_DIAG: (N, D), _lib.NOISE_SHARED: (D, D),
+            _lib.NOISE_PACKED: (N, D * (D + 1) // 2)}[code]
     if tuple(S.shape) != want:
         raise ValueError("noise_covars has shape %s, expected %s for layout %r" % (tuple(S.shape), want, layout))
     return S, code
@@ -256,7 +257,8 @@ class HostContext:
     def _data(self, X, S, noise):
         code = NOISE_LAYOUTS[noise] if isinstance(noise, str) else int(noise)
         N = X.shape[0]
-        want = {_lib.NOISE_FULL: (N, self.D, self.D), _lib.NOISE_DIAG: (N, self.D), _lib.NOISE_SHARED: (self.D, self.D)}
+        want = {_lib.NOISE_FULL: (N, self.D, self.D), _lib.NOISE_DIAG: (N, self.D), _lib.NOISE_SHARED: (self.D, self.D),
+                _lib.NOISE_PACKED: (N, self.D * (self.D + 1) // 2)}
         pX = self._host(X, "X", (N, self.D))
         pS = self._host(S, "noise_covars", want[code]) if code != _lib.NOISE_NONE else ctypes.c_void_p(0)
         return pX, pS, code, N
@@ -292,6 +294,65 @@ class HostContext:
             self._host(ll, "out_ll") if want_ll else ctypes.c_void_p(0), ctypes.byref(tot), ctypes.byref(bad)),
             "dgmm_score_host")
         return (tot.value, bad.value, ll) if want_ll else (tot.value, bad.value)
+
+
+    # ---- resident table: upload once, iterate many times ------------------------------------
+    def upload(self, X, S, noise="full", pack=False):
+        """Copies the table into device memory owned by the context (``dgmm_ctx_upload``); with ``pack`` a
+        full ``[N,D,D]`` noise tensor is packed to lower triangles on the device as it streams in."""
+        pX, pS, code, N = self._data(X, S, noise)
+        check(_lib.lib().dgmm_ctx_upload(self._ctx, pX, pS, code, N, 1 if pack else 0), "dgmm_ctx_upload")
+        self.n_resident = N
+        return self
+
+    def _params_host(self, alpha, mu, Sigma):
+        return (self._host(alpha, "alpha", (self.K,)), self._host(mu, "means", (self.K, self.D)),
+                self._host(Sigma, "covars", (self.K, self.D, self.D)))
+
+    def em_iteration_resident(self, w, alpha, mu, Sigma):
+        ll, bad = ctypes.c_double(0.0), ctypes.c_int64(0)
+        check(_lib.lib().dgmm_em_iteration_resident(self._ctx, float(w), *self._params_host(alpha, mu, Sigma),
+                                                    ctypes.byref(ll), ctypes.byref(bad)), "dgmm_em_iteration_resident")
+        return ll.value, bad.value
+
+    def em_fit_resident(self, max_iters, w, tol, alpha, mu, Sigma):
+        """``base.py:46-55`` on the resident table: returns ``(iterations done, ll trace, n_nonpd)``."""
+        done, bad = ctypes.c_int(0), ctypes.c_int64(0)
+        trace = (ctypes.c_double * max(int(max_iters), 1))()
+        check(_lib.lib().dgmm_em_fit_resident(self._ctx, int(max_iters), float(w), float(tol),
+                                              *self._params_host(alpha, mu, Sigma), ctypes.byref(done), trace,
+                                              ctypes.byref(bad)), "dgmm_em_fit_resident")
+        n = min(int(max_iters), done.value + 1)
+        return done.value, [trace[i] for i in range(n)], bad.value
+
+    def score_resident(self, alpha, mu, Sigma, want_ll=False):
+        ll = torch.empty(self.n_resident, dtype=torch.float32) if want_ll else None
+        tot, bad = ctypes.c_double(0.0), ctypes.c_int64(0)
+        check(_lib.lib().dgmm_score_resident(self._ctx, *self._params_host(alpha, mu, Sigma),
+                                             self._host(ll, "out_ll") if want_ll else ctypes.c_void_p(0),
+                                             ctypes.byref(tot), ctypes.byref(bad)), "dgmm_score_resident")
+        return (tot.value, bad.value, ll) if want_ll else (tot.value, bad.value)
+
+
+def pack_noise(S):
+    """``S [N,D,D]`` -> packed lower triangles ``[N, D(D+1)/2]`` (row-major: (0,0),(1,0),(1,1),(2,0),...), the
+    ``"packed"`` noise layout: CUDA tensors through ``dgmm_pack_noise_f32``, CPU tensors through the threaded
+    ``dgmm_pack_noise_host``."""
+    if S.dim() != 3 or S.shape[1] != S.shape[2]:
+        raise ValueError("expected [N,D,D], got %s" % (tuple(S.shape),))
+    N, D = S.shape[0], S.shape[1]
+    if S.dtype != torch.float32:
+        raise TypeError("noise_covars must be float32")
+    S = S.contiguous()
+    out = torch.empty(N, D * (D + 1) // 2, dtype=torch.float32, device=S.device)
+    if S.is_cuda:
+        with torch.cuda.device(S.device):
+            rc = _lib.lib().dgmm_pack_noise_f32(_ptr(S), N, D, _ptr(out), _stream(S.device))
+        check(rc, "dgmm_pack_noise_f32")
+    else:
+        check(_lib.lib().dgmm_pack_noise_host(ctypes.c_void_p(S.data_ptr()), N, D, ctypes.c_void_p(out.data_ptr())),
+              "dgmm_pack_noise_host")
+    return out
 
 
 # -----------------------------------------------------------------------------------------
@@ -405,6 +466,57 @@ def sgd_adam_step(stats, n_batch, n_total, w, lr, betas, eps, step, params, exp_
     check(rc, "dgmm_sgd_adam_step_f32")
 
 
+class SgdStepper:
+    """One minibatch of ``BaseSGDGMM.fit`` per ctypes call (``dgmm_sgd_fused_step_f32``): gather of the shuffled
+    batch from the resident table + fused statistics pass + Adam step.  Everything that does not change between
+    steps (pointers, shapes, workspace) is validated and marshalled ONCE here; ``step`` only passes the batch
+    offset, the step count and the learning rate.  At D = 10, K = 64 the host side of a step drops from three
+    wrapper calls with their argument checks (~0.1 ms) to one call."""
+
+    def __init__(self, X, S, noise, batch_size, params, exp_avg, exp_avg_sq, log_alpha, Sigma, epoch_acc, w, betas, eps):
+        X = _f32c(X, "X")
+        dev = X.device
+        N, D = X.shape
+        sw, mu, ld, ll = params
+        K = mu.shape[0]
+        S, code = _noise(S, noise, N, D, dev)
+        for n, t in (("soft_weights", sw), ("means", mu), ("l_diag", ld), ("l_lower", ll), ("log_alpha", log_alpha),
+                     ("Sigma", Sigma)) + tuple(("exp_avg", t) for t in exp_avg) + \
+                tuple(("exp_avg_sq", t) for t in exp_avg_sq):
+            _inplace(n, t)
+        if not (epoch_acc.is_cuda and epoch_acc.dtype == torch.float64 and epoch_acc.numel() == 2):
+            raise DgmmError("epoch_acc must be a float64 CUDA tensor of 2 elements")
+        self.dev, self.N, self.D, self.K, self.code = dev, N, D, K, code
+        B = int(batch_size)
+        per_point = code in (_lib.NOISE_FULL, _lib.NOISE_DIAG, _lib.NOISE_PACKED)
+        self.bufX = torch.empty(B, D, dtype=torch.float32, device=dev)
+        self.bufS = torch.empty((B,) + tuple(S.shape[1:]), dtype=torch.float32, device=dev) if per_point else None
+        self.ll = torch.empty(B, dtype=torch.float32, device=dev)
+        self.stats = torch.empty(stats_len(D, K), dtype=torch.float32, device=dev)
+        self.ws = workspace(D, K, dev)
+        arr = ctypes.c_void_p * 4
+        self._m = arr(*[t.data_ptr() if t.numel() else None for t in exp_avg])
+        self._v = arr(*[t.data_ptr() if t.numel() else None for t in exp_avg_sq])
+        self._keep = (X, S, params, exp_avg, exp_avg_sq, log_alpha, Sigma, epoch_acc)
+        self._head = (_ptr(X), _ptr(S), code, D, K)
+        self._bufs = (_ptr(self.bufX), _ptr(self.bufS), _ptr(self.ll))
+        self._tail = (_ptr(sw), _ptr(mu), _ptr(ld), _ptr(ll if D > 1 else None), self._m, self._v, _ptr(log_alpha),
+                      _ptr(Sigma), _ptr(epoch_acc), _ptr(self.ws), self.ws.numel())
+        self._stats_p = _ptr(self.stats)
+        self._hyper = (float(w), float(betas[0]), float(betas[1]), float(eps))
+        self._fn = _lib.lib().dgmm_sgd_fused_step_f32
+        self._stream = _stream(dev)
+
+    def step(self, perm, batch_lo, B, phase, n_batch, n_total, lr, step):
+        """``perm``: int64 CUDA permutation of the table rows (None: contiguous batch)."""
+        w, b1, b2, eps = self._hyper
+        with torch.cuda.device(self.dev):
+            rc = self._fn(*self._head, ctypes.c_void_p(perm.data_ptr()) if perm is not None else None, int(batch_lo),
+                          int(B), *self._bufs, int(phase), self._stats_p, float(n_batch), float(n_total), w, float(lr),
+                          b1, b2, eps, int(step), *self._tail, _stream(self.dev))
+        check(rc, "dgmm_sgd_fused_step_f32")
+
+
 # -----------------------------------------------------------------------------------------
 # posterior sampling (deconv/gmm/sgd_deconv_gmm.py:107-119) without [N,K,D,D] tensors
 # -----------------------------------------------------------------------------------------
@@ -499,8 +611,8 @@ def gather_points(X, S, idx, outX=None, outS=None):
         code = _lib.NOISE_NONE
     else:
         S = _f32c(S, "noise_covars", dev)
-        code = _lib.NOISE_FULL if S.dim() == 3 else _lib.NOISE_DIAG
-        if S.shape[0] != N or tuple(S.shape[1:]) not in ((D, D), (D,)):
+        code = _lib.NOISE_FULL if S.dim() == 3 else (_lib.NOISE_DIAG if S.shape[1] == D else _lib.NOISE_PACKED)
+        if S.shape[0] != N or tuple(S.shape[1:]) not in ((D, D), (D,), (D * (D + 1) // 2,)):
             raise ValueError("noise_covars has shape %s for X %s" % (tuple(S.shape), tuple(X.shape)))
     if outX is None:
         outX = torch.empty(B, D, dtype=torch.float32, device=dev)

@@ -12,7 +12,8 @@
  *   - plain C: pointers, sizes, a stream handle; no torch types.
  *   - all float32, row-major, exactly the reference's tensor layouts:
  *       X [N,D], noise S [N,D,D], means [K,D], covars [K,D,D].
- *   - "device" entry points take caller-owned DEVICE pointers, never allocate, and are
+ *   - "device" entry points take caller-owned DEVICE pointers, never allocate (one exception: for K > 256
+ *     the component-chunked passes take (n_chunks + 1) N floats from the stream-ordered allocator), and are
  *     asynchronous on `stream` (a cudaStream_t passed as void*; NULL = default stream).
  *     Workspace is caller-provided; query its size with dgmm_workspace_bytes().
  *   - "host" entry points (suffix _host) take HOST pointers, stage through device memory
@@ -40,9 +41,9 @@
 extern "C" {
 #endif
 
-#define DGMM_ABI_VERSION 1
+#define DGMM_ABI_VERSION 2
 #define DGMM_MAX_D 32
-#define DGMM_MAX_K 256
+#define DGMM_MAX_K 1024 /* one launch serves 256 components; larger K runs in component chunks (see dgmm_estep_stats_f32) */
 
 /* error codes (negative) */
 #define DGMM_OK 0
@@ -60,6 +61,9 @@ extern "C" {
 #define DGMM_NOISE_DIAG 1   /* S [N,D]   = diagonal of each S_i                          */
 #define DGMM_NOISE_NONE 2   /* S ignored (S_i = 0): SGDGMMModule.forward, sgd_gmm.py:49-62 */
 #define DGMM_NOISE_SHARED 3 /* S [D,D]   one matrix for all points (data_gen.py:50-53)   */
+#define DGMM_NOISE_PACKED 4 /* S [N,D(D+1)/2] lower triangle of each S_i, row-major: (0,0),(1,0),(1,1),(2,0)...
+                             * the same information as DGMM_NOISE_FULL in 1.7-1.9x fewer bytes (HBM, PCIe and the
+                             * kernels' shared-memory ring); dgmm_pack_noise_f32 / dgmm_pack_noise_host convert */
 
 /* Packed statistics buffer written by dgmm_estep_stats_f32.
  *   [ s0 (K) | s1 (K*D) | S2 (K*D*D, full symmetric) | ll_hi | ll_lo | sum_g | nonpd ]
@@ -106,6 +110,10 @@ DGMM_API int dgmm_loglik_f32(const float* X, const float* S, int noise_layout, i
  * Replaces deconv/gmm/deconv_gmm.py:39-107 (E-step + the reductions of the M-step),
  * deconv/gmm/batch_deconv_gmm.py:95-120, deconv/gmm/online_deconv_gmm.py:148-166 and the
  * autograd backward of deconv/gmm/sgd_deconv_gmm.py:14-28 (deconv/gmm/sgd_gmm.py:181).
+ * K > 256 (the reference's Gaia runs use K = 512, experiments/gmm/gaia/variable_k/fit_em.sh:18): the components
+ * are served in chunks of <= 256 - a log-likelihood pass per chunk, ll_i = logsumexp over the chunks, then a
+ * statistics pass per chunk weighted with g_i exp(ll_chunk,i - ll_i), which makes omega_ij exact; a non-zero
+ * resp_floor is scaled by the chunk's share of the point.
  *   g [N] optional per-point weights (NULL = 1; = grad_output for the SGD backward);
  *   resp_floor: 0 for EM/SGD, 10*eps for OnlineDeconvGMM (online_deconv_gmm.py:150);
  *   out_ll [N] optional (required where dgmm_stats_needs_ll says so: DGMM_ERR_LL_REQUIRED otherwise);
@@ -186,6 +194,32 @@ DGMM_API int dgmm_score_host(dgmm_ctx* ctx, const float* X, const float* S, int 
                     const float* alpha, const float* mu, const float* Sigma,
                     float* out_ll, double* ll_sum, int64_t* nonpd);
 
+/* ---- resident table: upload once, iterate many times --------------------------------------
+ * The per-call entries above re-send the whole table every EM iteration (the reference's contract: fit() is
+ * handed host tensors).  A fit of E iterations should pay the PCIe transfer once: dgmm_ctx_upload copies the
+ * table into device memory owned by the context (chunked, from pageable or pinned host memory) and the
+ * _resident entries iterate on that copy.  With pack_full != 0 a DGMM_NOISE_FULL table is packed on the
+ * device while it streams in (kept as DGMM_NOISE_PACKED: 1.7-1.9x less HBM).  One table per context; a second
+ * upload replaces it.  Replaces the loop of deconv/gmm/base.py:46-55 around data that stays on the GPU. */
+DGMM_API int dgmm_ctx_upload(dgmm_ctx* ctx, const float* X, const float* S, int noise_layout, int64_t N,
+                             int pack_full);
+/* One EM iteration on the resident table; alpha/mu/Sigma are HOST in/out exactly as in dgmm_em_iteration_host. */
+DGMM_API int dgmm_em_iteration_resident(dgmm_ctx* ctx, float w, float* alpha, float* mu, float* Sigma,
+                                        double* ll_sum, int64_t* nonpd);
+/* E iterations of base.py:46-55 on the resident table without a host round trip of the parameters in between:
+ * stops when |ll - ll_prev| < tol or a non-PD pair appears (base.py:48-53); *iters_done and ll_trace[0..E)
+ * (optional) report what ran.  Parameters are uploaded once and read back once. */
+DGMM_API int dgmm_em_fit_resident(dgmm_ctx* ctx, int max_iters, float w, double tol, float* alpha, float* mu,
+                                  float* Sigma, int* iters_done, double* ll_trace, int64_t* nonpd);
+/* sum_i ll_i (and optionally ll_i [N] on the host) on the resident table. */
+DGMM_API int dgmm_score_resident(dgmm_ctx* ctx, const float* alpha, const float* mu, const float* Sigma,
+                                 float* out_ll, double* ll_sum, int64_t* nonpd);
+
+/* ---- noise layout converters ---------------------------------------------------------------- */
+/* S_full [N,D,D] -> S_packed [N,D(D+1)/2] (lower triangles, row-major).  Device pointers / host pointers. */
+DGMM_API int dgmm_pack_noise_f32(const float* S_full, int64_t N, int D, float* S_packed, void* stream);
+DGMM_API int dgmm_pack_noise_host(const float* S_full, int64_t N, int D, float* S_packed);
+
 /* ---- initialisation: fused k-means assignment (device pointers) ----------------------- */
 
 /* Packed buffer written by dgmm_kmeans_assign_f32:
@@ -222,7 +256,7 @@ DGMM_API int dgmm_kmeans_update_f32(int mode, const float* stats, int D, int K, 
 /* ---- device-resident minibatches --------------------------------------------------------- */
 
 /* Gathers the rows idx[0..B) (int64, device) of X [N,D] and of the noise table (DGMM_NOISE_FULL: [N,D,D],
- * DGMM_NOISE_DIAG: [N,D], DGMM_NOISE_NONE: nothing) into contiguous outX [B,D] / outS [B,...] in one launch.
+ * DGMM_NOISE_PACKED: [N,D(D+1)/2], DGMM_NOISE_DIAG: [N,D], DGMM_NOISE_NONE: nothing) into contiguous outX [B,D] / outS [B,...] in one launch.
  * Replaces the DataLoader's per-sample __getitem__ + collate (deconv/gmm/data.py:7-17,
  * deconv/gmm/sgd_gmm.py:139-145, deconv/gmm/online_deconv_gmm.py:43-56) for tables resident on the GPU. */
 DGMM_API int dgmm_gather_points_f32(const float* X, const float* S, int noise_layout, const int64_t* idx, int64_t B,
@@ -281,6 +315,23 @@ DGMM_API int dgmm_sgd_adam_step_f32(const float* stats, double n_batch, double n
                                     float* soft_weights, float* means, float* l_diag, float* l_lower,
                                     float* const* exp_avg, float* const* exp_avg_sq, float* log_alpha,
                                     float* Sigma, double* epoch_acc, void* stream);
+
+/* One minibatch of BaseSGDGMM.fit (deconv/gmm/sgd_gmm.py:167-182) in ONE call: gather of the shuffled batch from
+ * the resident table (the DataLoader's __getitem__ + collate, :139-145,167-169), fused statistics pass (forward +
+ * backward, :173-181) and the Adam step of dgmm_sgd_adam_step_f32 (:182).
+ *   X / S: the resident table (layout as noise_layout); perm: device int64 permutation of its rows, the batch is
+ *   perm[batch_lo .. batch_lo + B) (perm == NULL: the contiguous rows batch_lo .. batch_lo + B);
+ *   bufX [B,D], bufS [B,...]: gather outputs (unused without perm); ll_scratch [B] or NULL (needed when
+ *   dgmm_stats_needs_ll); phase: 1 = gather + statistics into `stats` (then the caller all-reduces it),
+ *   2 = Adam step from `stats`, 3 = both (single process).  Remaining arguments as dgmm_sgd_adam_step_f32. */
+DGMM_API int dgmm_sgd_fused_step_f32(const float* X, const float* S, int noise_layout, int D, int K,
+                                     const int64_t* perm, int64_t batch_lo, int64_t B, float* bufX, float* bufS,
+                                     float* ll_scratch, int phase, float* stats, double n_batch, double n_total,
+                                     float w, float lr, float beta1, float beta2, float eps, int step,
+                                     float* soft_weights, float* means, float* l_diag, float* l_lower,
+                                     float* const* exp_avg, float* const* exp_avg_sq, float* log_alpha,
+                                     float* Sigma, double* epoch_acc, void* workspace, size_t workspace_bytes,
+                                     void* stream);
 
 /* ---- diagnostics (not part of the drop-in surface) ----------------------------------- */
 

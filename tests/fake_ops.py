@@ -32,6 +32,12 @@ def _full_noise(X, S, noise):
         return out
     if noise == "shared":
         return np.broadcast_to(_np(S), (N, D, D)).copy()
+    if noise == "packed":
+        ia, ib = np.tril_indices(D)
+        out = np.zeros((N, D, D))
+        out[:, ia, ib] = _np(S)
+        out[:, ib, ia] = _np(S)
+        return out
     return np.zeros((N, D, D))
 
 

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), s
     lib.dgmm_abi_version.restype = ctypes.c_int
-    assert lib.dgmm_abi_version() == 1
+    assert lib.dgmm_abi_version() == 2
     n = ctypes.c_int(0)
     dims = (ctypes.c_int * 32)()
     assert lib.dgmm_supported_dims(dims, ctypes.byref(n)) == 0

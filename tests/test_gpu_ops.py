@@ -45,6 +45,9 @@ def run_case(ops, N, D, K, seed, noise="full", with_g=False, floor=0.0):
     if noise == "diag":
         Sd = np.stack([np.diag(np.diag(s)) for s in S])
         S_or, S_dev = Sd, np.stack([np.diag(s) for s in S])
+    elif noise == "packed":
+        ia, ib = np.tril_indices(D)
+        S_or, S_dev = S, S[:, ia, ib]
     else:
         S_or, S_dev = S, S
     tX, tS, tmu, tSg = to_dev(X, S_dev, mu, Sigma)

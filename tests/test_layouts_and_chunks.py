@@ -1,0 +1,260 @@
+"""Round-2 surface of the C ABI, on the GPU against the float64 oracle:
+
+* the packed lower-triangular noise layout ``[N, D(D+1)/2]`` at every D (pair kernels, cooperative kernels,
+  materialising / sampling kernels, the gather kernel, the host pipeline, the converters);
+* K > 256 through component chunks (the reference's Gaia runs use K = 512:
+  experiments/gmm/gaia/variable_k/fit_em.sh:18);
+* the resident-table host entries (``dgmm_ctx_upload`` + ``dgmm_em_fit_resident``);
+* the re-mapped materialising E-step kernel at ragged N.
+
+Tolerances (north_star): 1e-4 relative on the mean log-likelihood, 1e-3 on statistics / parameters."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import gmm_oracle as orc
+from helpers import synth, rel
+from test_gpu_ops import run_case, to_dev, dev, LL_RTOL, STAT_RTOL
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from density_deconvolution_b200 import ops as o
+    o.set_tuning()
+    return o
+
+
+def tril(S):
+    D = S.shape[-1]
+    ia, ib = np.tril_indices(D)
+    return np.ascontiguousarray(S[..., ia, ib])
+
+
+# ---- packed noise ------------------------------------------------------------------------------------
+@pytest.mark.parametrize("D", list(range(1, 33)))
+def test_packed_noise_every_dimension(ops, D):
+    K = 5 if D % 3 else 40
+    run_case(ops, N=131 if D <= 16 else 45, D=D, K=K, seed=7000 + D, noise="packed", with_g=(D % 2 == 1))
+
+
+@pytest.mark.parametrize("D,K", [(10, 64), (16, 128), (9, 128), (7, 200), (13, 33), (4, 256), (20, 64), (32, 70)])
+def test_packed_equals_full_layout(ops, D, K):
+    """Same inputs in both layouts: identical per-point log-likelihoods and statistics to float32 rounding."""
+    rng = np.random.default_rng(7100 + D + K)
+    N = 777 if D <= 16 else 61
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    tX, tS, tP, tmu, tSg = to_dev(X, S, tril(S), mu, Sigma)
+    tla = torch.tensor(np.log(alpha), dtype=torch.float32, device=dev())
+    ll_f, st_f = ops.estep_stats(tX, tS, tla, tmu, tSg, noise="full")
+    ll_p, st_p = ops.estep_stats(tX, tP, tla, tmu, tSg, noise="packed")
+    np.testing.assert_allclose(ll_p.cpu().numpy(), ll_f.cpu().numpy(), rtol=3e-6, atol=3e-6)
+    scale = st_f.abs().max().item()
+    assert (st_p - st_f).abs().max().item() <= 2e-5 * scale
+    l1 = ops.loglik(tX, tS, tla, tmu, tSg, noise="full")
+    l2 = ops.loglik(tX, tP, tla, tmu, tSg, noise="packed")
+    np.testing.assert_allclose(l2.cpu().numpy(), l1.cpu().numpy(), rtol=3e-6, atol=3e-6)
+
+
+def test_packed_unaligned_and_ragged(ops):
+    """Base pointers that are not 16-byte aligned take the cooperative (non-TMA) tile loads."""
+    D, K = 10, 64
+    rng = np.random.default_rng(7200)
+    for N in (1, 5, 63, 130):
+        X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+        ND = D * (D + 1) // 2
+        bufP = torch.zeros(N * ND + 1, dtype=torch.float32, device=dev())
+        bufX = torch.zeros(N * D + 1, dtype=torch.float32, device=dev())
+        tP = bufP[1:].view(N, ND)
+        tX = bufX[1:].view(N, D)
+        tP.copy_(torch.tensor(tril(S), dtype=torch.float32))
+        tX.copy_(torch.tensor(X, dtype=torch.float32))
+        assert tP.data_ptr() % 16 != 0
+        tmu, tSg = to_dev(mu, Sigma)
+        tla = torch.tensor(np.log(alpha), dtype=torch.float32, device=dev())
+        ll = ops.loglik(tX, tP, tla, tmu, tSg, noise="packed").cpu().numpy()
+        want = orc.loglik(X, S, alpha, mu, Sigma)
+        assert np.max(np.abs(ll - want)) <= 2e-4 * max(1.0, np.max(np.abs(want)))
+
+
+def test_pack_noise_converters(ops):
+    rng = np.random.default_rng(7300)
+    for D, N in ((1, 5), (3, 17), (10, 1000), (16, 70000), (32, 33)):
+        S = rng.standard_normal((N, D, D)).astype(np.float32)
+        want = tril(S)
+        got_h = ops.pack_noise(torch.tensor(S))
+        got_d = ops.pack_noise(torch.tensor(S, device=dev()))
+        assert np.array_equal(got_h.numpy(), want)
+        assert np.array_equal(got_d.cpu().numpy(), want)
+
+
+def test_packed_gather_full_sample_and_logprob(ops):
+    D, K, N = 5, 7, 40
+    rng = np.random.default_rng(7400)
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    tX, tS, tP, tmu, tSg = to_dev(X, S, tril(S), mu, Sigma)
+    tla = torch.tensor(np.log(alpha), dtype=torch.float32, device=dev())
+    idx = torch.tensor(rng.permutation(N)[:23], device=dev())
+    gx, gs = ops.gather_points(tX, tP, idx)
+    assert torch.equal(gx, tX[idx]) and torch.equal(gs, tP[idx])
+    a = ops.estep_full(tX, tS, tla, tmu, tSg, noise="full")
+    b = ops.estep_full(tX, tP, tla, tmu, tSg, noise="packed")
+    for u, v in zip(a[:4], b[:4]):
+        np.testing.assert_allclose(v.cpu().numpy(), u.cpu().numpy(), rtol=1e-5, atol=1e-5)
+    M = 3
+    u = torch.rand(N, M, device=dev())
+    z = torch.randn(N, M, D, device=dev())
+    s_full = ops.posterior_sample(tX, tS, tla, tmu, tSg, u, z, noise="full")[0]
+    s_pack = ops.posterior_sample(tX, tP, tla, tmu, tSg, u, z, noise="packed")[0]
+    np.testing.assert_allclose(s_pack.cpu().numpy(), s_full.cpu().numpy(), rtol=1e-5, atol=1e-5)
+    V = torch.randn(N, M, D, device=dev())
+    p_full = ops.posterior_logprob(tX, tS, tla, tmu, tSg, V, noise="full")[0]
+    p_pack = ops.posterior_logprob(tX, tP, tla, tmu, tSg, V, noise="packed")[0]
+    np.testing.assert_allclose(p_pack.cpu().numpy(), p_full.cpu().numpy(), rtol=1e-5, atol=1e-4)
+
+
+def test_estimators_accept_packed_noise():
+    from density_deconvolution_b200 import DeconvGMM, SGDDeconvGMM, ops
+    D, K, N = 4, 3, 200
+    rng = np.random.default_rng(7500)
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    tX, tS = to_dev(X, S)
+    tP = ops.pack_noise(tS)
+    fits = []
+    for noise in (tS, tP):
+        m = DeconvGMM(K, D, epochs=4, w=1e-3, tol=0.0, device=dev())
+        m.set_params(alpha, mu, Sigma)
+        m.fit((tX, noise), init=False)
+        fits.append(m)
+    assert rel(fits[1].means.cpu().numpy(), fits[0].means.cpu().numpy()) < 1e-5
+    assert rel(fits[1].covars.cpu().numpy(), fits[0].covars.cpu().numpy()) < 1e-5
+    sg = SGDDeconvGMM(K, D, epochs=2, batch_size=50, lr=1e-2, k_means_iters=2, device=dev())
+    sg.fit((tX, tP))
+    assert np.isfinite(sg.score_batch((tX, tP)))
+
+
+# ---- K > 256: component chunks -----------------------------------------------------------------------
+@pytest.mark.parametrize("D,K", [(7, 257), (7, 384), (7, 512), (16, 257), (16, 384), (16, 512), (3, 1024), (20, 300)])
+def test_component_chunks(ops, D, K):
+    N = 150 if D <= 16 else 40
+    run_case(ops, N=N, D=D, K=K, seed=8000 + D + K, with_g=(K % 2 == 0))
+
+
+def test_component_chunks_noise_layouts_and_floor(ops):
+    run_case(ops, N=90, D=5, K=300, seed=8100, noise="diag")
+    run_case(ops, N=90, D=6, K=300, seed=8101, noise="packed")
+    # a responsibility floor is scaled by the chunk's share of each point: bounded deviation, documented
+    D, K, N, floor = 4, 320, 120, 10 * np.finfo(np.float32).eps
+    rng = np.random.default_rng(8102)
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    tX, tS, tmu, tSg = to_dev(X, S, mu, Sigma)
+    tla = torch.tensor(np.log(alpha), dtype=torch.float32, device=dev())
+    _, st = ops.estep_stats(tX, tS, tla, tmu, tSg, resp_floor=float(floor))
+    d0 = ops.unpack_stats(st, D, K)[0].cpu().numpy().astype(np.float64)
+    lo = orc.suff_stats(X, S, alpha, mu, Sigma, resp_floor=0.0)[0]
+    hi = orc.suff_stats(X, S, alpha, mu, Sigma, resp_floor=floor)[0]
+    assert np.all(d0 >= lo * (1 - 1e-3) - 1e-9) and np.all(d0 <= hi * (1 + 1e-3) + 1e-9)
+
+
+def test_component_chunks_em_fit_and_full(ops):
+    """EM iterations and the materialising E-step at K = 300 track the oracle."""
+    from density_deconvolution_b200 import DeconvGMM
+    D, K, N = 3, 300, 900
+    rng = np.random.default_rng(8200)
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    m = DeconvGMM(K, D, epochs=2, w=1e-3, tol=0.0, device=dev())
+    m.set_params(alpha, mu, Sigma)
+    tX, tS = to_dev(X, S)
+    m.fit((tX, tS), init=False)
+    a, mm, Sg = alpha, mu, Sigma
+    for _ in range(2):
+        s0, s1, S2, ll = orc.suff_stats(X, S, a, mm, Sg)
+        w_new, mm, Sg = orc.m_step_from_stats(s0, s1, S2, mm, Sg, N, 1e-3)
+        a = w_new[:, 0]
+    assert rel(m.means.cpu().numpy(), mm) < 1e-3 and rel(m.covars.cpu().numpy(), Sg) < 1e-3
+    assert rel(m.weights.cpu().numpy()[:, 0], a) < 1e-3
+    ll_sum, (log_r, b, B) = m._e_step((tX[:50], tS[:50]))
+    _, (lr, bb, BB), ll_o = orc.e_step(X[:50], S[:50], a, mm, Sg)
+    assert abs(ll_sum.item() - ll_o.sum()) <= 5e-4 * abs(ll_o.sum())
+    assert np.max(np.abs(np.exp(log_r.cpu().numpy()) - np.exp(lr))) < 2e-3
+
+
+def test_nonpd_is_reported_through_chunks(ops):
+    D, K, N = 3, 300, 20
+    rng = np.random.default_rng(8300)
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    Sigma = Sigma.copy()
+    Sigma[290] = -np.eye(D)               # a non-PD component in the second chunk
+    tX, tS, tmu, tSg = to_dev(X, S, mu, Sigma)
+    tla = torch.tensor(np.log(alpha), dtype=torch.float32, device=dev())
+    _, sums = ops.loglik(tX, tS, tla, tmu, tSg, want_sum=True)
+    assert sums[1].item() > 0
+    _, st = ops.estep_stats(tX, tS, tla, tmu, tSg)
+    assert st[-1].item() > 0
+
+
+# ---- resident table ----------------------------------------------------------------------------------
+@pytest.mark.parametrize("D,K,noise,pack", [(10, 64, "full", False), (10, 64, "full", True), (16, 128, "packed", False),
+                                            (5, 6, "diag", False), (3, 4, "shared", False), (4, 5, "none", False),
+                                            (20, 30, "full", True), (6, 300, "full", True)])
+def test_resident_fit_equals_per_call_host_iterations(ops, D, K, noise, pack):
+    N = 3000 if D <= 16 else 300
+    rng = np.random.default_rng(9000 + D + K)
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    hX = torch.tensor(X, dtype=torch.float32)
+    if noise == "full":
+        hS = torch.tensor(S, dtype=torch.float32)
+    elif noise == "packed":
+        hS = torch.tensor(tril(S), dtype=torch.float32)
+    elif noise == "diag":
+        hS = torch.tensor(np.stack([np.diag(s) for s in S]), dtype=torch.float32)
+    elif noise == "shared":
+        hS = torch.tensor(S[0], dtype=torch.float32)
+    else:
+        hS = None
+    f = lambda a: torch.tensor(a, dtype=torch.float32).contiguous()  # noqa: E731
+    ctx = ops.HostContext(D, K, chunk_points=1024, device=0)
+    try:
+        a1, m1, S1 = f(alpha), f(mu), f(Sigma)
+        lls = []
+        for _ in range(3):
+            ll, bad = ctx.em_iteration(hX, hS, 1e-3, a1, m1, S1, noise=noise)
+            assert bad == 0
+            lls.append(ll)
+        a2, m2, S2 = f(alpha), f(mu), f(Sigma)
+        ctx.upload(hX, hS, noise=noise, pack=pack)
+        done, trace, bad = ctx.em_fit_resident(3, 1e-3, 0.0, a2, m2, S2)
+        assert done == 3 and bad == 0
+        np.testing.assert_allclose(trace, lls, rtol=2e-6)
+        assert rel(m2.numpy(), m1.numpy()) < 2e-5 and rel(S2.numpy(), S1.numpy()) < 2e-5
+        assert rel(a2.numpy(), a1.numpy()) < 2e-5
+        tot, bad, ll = ctx.score_resident(a2, m2, S2, want_ll=True)
+        tot_h, _ = ctx.score(hX, hS, a2, m2, S2, noise=noise)
+        assert abs(tot - tot_h) <= 1e-6 * abs(tot_h) and ll.shape == (N,)
+        # single-iteration entry + tolerance stop
+        ll1, _ = ctx.em_iteration_resident(1e-3, f(alpha), f(mu), f(Sigma))
+        assert abs(ll1 - lls[0]) <= 2e-6 * abs(lls[0])
+        done, trace, _ = ctx.em_fit_resident(50, 1e-3, 1e30, f(alpha), f(mu), f(Sigma))
+        assert done == 2          # the first comparison is against -inf (base.py:44,52), the second one stops
+    finally:
+        ctx.close()
+
+
+# ---- materialising E-step: block = component x 128 points -----------------------------------------------
+@pytest.mark.parametrize("N,D,K", [(1, 3, 4), (127, 5, 3), (128, 10, 7), (129, 10, 64), (300, 16, 5), (257, 17, 3),
+                                   (70, 32, 4), (513, 1, 2), (260, 9, 70)])
+def test_estep_full_ragged_shapes(ops, N, D, K):
+    rng = np.random.default_rng(9500 + N + D + K)
+    X, S, alpha, mu, Sigma = synth(rng, N, D, K)
+    tX, tS, tmu, tSg = to_dev(X, S, mu, Sigma)
+    tla = torch.tensor(np.log(alpha), dtype=torch.float32, device=dev())
+    ll, log_r, b, B, status = ops.estep_full(tX, tS, tla, tmu, tSg)
+    _, (lr, bb, BB), ll_o = orc.e_step(X, S, alpha, mu, Sigma)
+    assert int(status.item()) == 0
+    assert np.max(np.abs(ll.cpu().numpy() - ll_o)) <= 2e-4 * max(1.0, np.max(np.abs(ll_o)))
+    assert np.max(np.abs(np.exp(log_r.cpu().numpy()) - np.exp(lr))) < 1e-4
+    assert rel(b.cpu().numpy(), bb) < 1e-3
+    Bd = B.cpu().numpy()
+    assert np.max(np.abs(Bd - BB)) <= 1e-3 * np.max(np.abs(BB)) + 2e-5 * np.max(np.abs(Sigma))
+    assert np.array_equal(Bd, np.swapaxes(Bd, 2, 3))

@@ -77,7 +77,7 @@ def test_fused_and_autograd_routes_agree(device):
 
 # ---- the two kernels against the oracle ---------------------------------------------------------
 @pytest.mark.gpu
-@pytest.mark.parametrize("D,K", [(1, 3), (2, 1), (3, 4), (10, 64), (16, 128), (32, 256), (9, 200)])
+@pytest.mark.parametrize("D,K", [(1, 3), (2, 1), (3, 4), (10, 64), (16, 128), (32, 256), (9, 200), (7, 512), (4, 1000)])
 def test_adam_step_kernel(D, K):
     from density_deconvolution_b200 import ops
     dev = torch.device("cuda", 0)
