@@ -244,29 +244,52 @@ __global__ void kmeans_update_kernel(int mode, const float* __restrict__ stats, 
 // Minibatch gather for the device-resident batch iterator: rows idx[b] of X [N,D] and
 // of the noise table [N,n_s] (n_s = D*D, D or 0) -> contiguous outX [B,D], outS [B,n_s], one launch.
 // Replaces the per-sample __getitem__ + collate of the reference's DataLoader
-// (deconv/gmm/data.py:7-17, sgd_gmm.py:139-145).  One warp per point; 128-bit copies when the rows allow.
-__global__ void gather_points_kernel(const float* __restrict__ X, const float* __restrict__ S,
-                                     const long long* __restrict__ idx, long long B, int D, int n_s,
-                                     float* __restrict__ outX, float* __restrict__ outS) {
-    const int lane = threadIdx.x & 31;
-    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-    const bool vec = (n_s & 3) == 0 && ((((uintptr_t)S) | ((uintptr_t)outS)) & 15) == 0;
-    for (long long b = warp; b < B; b += nwarps) {
-        const long long i = idx[b];
-        const float* xs = X + (size_t)i * D;
-        float* xd = outX + (size_t)b * D;
-        for (int a = lane; a < D; a += 32) xd[a] = __ldg(xs + a);
-        if (n_s == 0) continue;
-        const float* ss = S + (size_t)i * n_s;
-        float* sd = outS + (size_t)b * n_s;
-        if (vec) {
-            const float4* s4 = reinterpret_cast<const float4*>(ss);
-            float4* d4 = reinterpret_cast<float4*>(sd);
-            for (int a = lane; a < n_s / 4; a += 32) d4[a] = __ldg(s4 + a);
-        } else {
-            for (int a = lane; a < n_s; a += 32) sd[a] = __ldg(ss + a);
+// (deconv/gmm/data.py:7-17, sgd_gmm.py:139-145).  128-bit copies when the rows allow.
+// Flat grid-stride copy: element e of the batch's noise block maps to (point b = e / n4, 16-byte chunk c = e % n4);
+// four independent loads are in flight per thread before the first store (the copy is latency-bound otherwise:
+// one warp per point left 25 of 32 lanes with a single 16-byte load each at D = 10).
+__global__ void __launch_bounds__(256) gather_points_kernel(const float* __restrict__ X, const float* __restrict__ S,
+                                                            const long long* __restrict__ idx, long long B, int D, int n_s,
+                                                            float* __restrict__ outX, float* __restrict__ outS) {
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nth = (long long)gridDim.x * blockDim.x;
+    const bool vec = n_s > 0 && (n_s & 3) == 0 && ((((uintptr_t)S) | ((uintptr_t)outS)) & 15) == 0;
+    if (vec) {
+        const int n4 = n_s >> 2;
+        const long long total = B * n4;
+        const float4* S4 = reinterpret_cast<const float4*>(S);
+        float4* O4 = reinterpret_cast<float4*>(outS);
+        long long e = tid;
+        for (; e + 3 * nth < total; e += 4 * nth) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long long ee = e + u * nth;
+                const long long b = ee / n4;
+                const int c = (int)(ee - b * n4);
+                v[u] = __ldg(S4 + idx[b] * n4 + c);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) O4[e + u * nth] = v[u];
         }
+        for (; e < total; e += nth) {
+            const long long b = e / n4;
+            const int c = (int)(e - b * n4);
+            O4[e] = __ldg(S4 + idx[b] * n4 + c);
+        }
+    } else if (n_s > 0) {
+        const long long total = B * n_s;
+        for (long long e = tid; e < total; e += nth) {
+            const long long b = e / n_s;
+            const int c = (int)(e - b * n_s);
+            outS[e] = __ldg(S + idx[b] * n_s + c);
+        }
+    }
+    const long long totalX = B * D;
+    for (long long e = tid; e < totalX; e += nth) {
+        const long long b = e / D;
+        const int a = (int)(e - b * D);
+        outX[e] = __ldg(X + idx[b] * D + a);
     }
 }
 
@@ -340,8 +363,8 @@ int dgmm_gather_points_f32(const float* X, const float* S, int noise_layout, con
     int sms = 0, optin = 0;
     int rc = km_device(&sms, &optin);
     if (rc) return rc;
-    const long long want = (B + 7) / 8;                       // 8 warps per block, one point per warp and trip
-    const int grid = (int)std::min<long long>(want, (long long)sms * 16);
+    const long long work = B * std::max(n_s / 4, D);          // ~ one 16-byte chunk per thread and trip
+    const int grid = (int)std::max<long long>(1, std::min<long long>((work + 1023) / 1024, (long long)sms * 8));
     gather_points_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, S, (const long long*)idx, (long long)B, D, n_s,
                                                                  outX, outS);
     CUDA_TRY(cudaGetLastError());
