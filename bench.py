@@ -631,23 +631,38 @@ def run_sgd(args, env, wl, X, S, fresh, n_steps=20):
             est.module.l_lower.copy_(L[:, idx[0], idx[1]])
         return est
 
-    make().fit((X[:min(3 * B, n_sub)], S[:min(3 * B, n_sub)]), init=False)       # warm-up (3 steps)
-    est = make()
-    env.barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    est.fit((X[:n_sub], S[:n_sub]), init=False)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    env.barrier()
-    if world > 1:
-        env.dist.all_reduce(ms, op=env.dist.ReduceOp.MAX)
-    t = ms.item() * 1e-3
-    return dict(api="SGDDeconvGMM.fit (1 epoch, device-resident batches, shuffle on device)",
-                batch_per_gpu=B, global_batch=B * world, steps=n_steps, ms_per_step=t / n_steps * 1e3,
-                steps_per_sec=n_steps / t, points_per_sec=float(n_sub) * world / t,
-                pair_evals_per_sec=float(n_sub) * world * K / t, mean_loglik=est.train_loss_curve[-1])
+    def timed_fit(peer):
+        w_est = make()
+        w_est.peer_reduce = peer
+        w_est.fit((X[:min(3 * B, n_sub)], S[:min(3 * B, n_sub)]), init=False)       # warm-up (3 steps)
+        est = make()
+        est.peer_reduce = peer
+        est._peers = getattr(w_est, "_peers", None)      # the symmetric buffer is set up once (collective), outside the timing
+        env.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        est.fit((X[:n_sub], S[:n_sub]), init=False)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        env.barrier()
+        if world > 1:
+            env.dist.all_reduce(ms, op=env.dist.ReduceOp.MAX)
+        return ms.item() * 1e-3, est
+
+    t, est = timed_fit(True)
+    used_peers = getattr(est, "_peers", None) is not None
+    out = dict(api="SGDDeconvGMM.fit (1 epoch, device-resident batches, shuffle on device)",
+               batch_per_gpu=B, global_batch=B * world, steps=n_steps, ms_per_step=t / n_steps * 1e3,
+               steps_per_sec=n_steps / t, points_per_sec=float(n_sub) * world / t,
+               pair_evals_per_sec=float(n_sub) * world * K / t, mean_loglik=est.train_loss_curve[-1],
+               reduction=("none (one GPU)" if world == 1 else
+                          "fused into the Adam kernels over NVLink peer memory (dgmm_sgd_adam_step_peers_f32)" if used_peers
+                          else "NCCL all-reduce between the statistics pass and the Adam kernels"))
+    if world > 1 and used_peers:
+        t2, est2 = timed_fit(False)
+        out["nccl_allreduce_variant"] = dict(ms_per_step=t2 / n_steps * 1e3, mean_loglik=est2.train_loss_curve[-1])
+    return out
 
 
 def host_mem_available():

@@ -32,7 +32,7 @@ SYMBOLS = (
     "dgmm_ctx_upload", "dgmm_em_iteration_resident", "dgmm_em_fit_resident", "dgmm_score_resident",
     "dgmm_pack_noise_f32", "dgmm_pack_noise_host",
     "dgmm_kmeans_workspace_bytes", "dgmm_kmeans_assign_f32", "dgmm_kmeans_update_f32",
-    "dgmm_gather_points_f32", "dgmm_posterior_sample_f32", "dgmm_posterior_logprob_f32", "dgmm_sgd_params_f32", "dgmm_sgd_adam_step_f32", "dgmm_sgd_fused_step_f32",
+    "dgmm_gather_points_f32", "dgmm_posterior_sample_f32", "dgmm_posterior_logprob_f32", "dgmm_sgd_params_f32", "dgmm_sgd_adam_step_f32", "dgmm_sgd_fused_step_f32", "dgmm_sgd_adam_step_peers_f32",
     "dgmm_debug_set_tuning", "dgmm_debug_get_plan", "dgmm_debug_pair_timing", "dgmm_debug_pair_times",
 )
 
@@ -136,6 +136,10 @@ def lib():
     L.dgmm_sgd_fused_step_f32.argtypes = [vp, vp, i32, i32, i32, vp, i64, i64, vp, vp, vp, i32, vp, f64, f64, f32, f32,
                                           f32, f32, f32, i32, vp, vp, vp, vp, ctypes.POINTER(vp), ctypes.POINTER(vp),
                                           vp, vp, vp, vp, sz, vp]
+    L.dgmm_sgd_adam_step_peers_f32.restype = i32
+    L.dgmm_sgd_adam_step_peers_f32.argtypes = [ctypes.POINTER(vp), i32, i32, i64, i64, ctypes.c_uint32, vp, f64, f64,
+                                               f32, f32, f32, f32, f32, i32, i32, i32, vp, vp, vp, vp,
+                                               ctypes.POINTER(vp), ctypes.POINTER(vp), vp, vp, vp, vp]
     L.dgmm_debug_set_tuning.restype = i32
     L.dgmm_debug_set_tuning.argtypes = [i32] * 8
     L.dgmm_debug_get_plan.restype = i32

@@ -34,6 +34,60 @@ struct AdamCfg {
     float bc1, bc2_sqrt;  // 1 - beta1^t, sqrt(1 - beta2^t)
 };
 
+// Cross-GPU reduction fused into the consumer (round 2).  Under one process per GPU every rank's packed statistics
+// sit in a SYMMETRIC buffer that all peers map over NVLink (torch.distributed._symmetric_memory is only the
+// allocator / handle exchange).  Instead of an NCCL all-reduce between the statistics pass and the Adam kernels
+// (a separate collective kernel on another stream, ~100 us per step at 140 KB), the two Adam kernels read the
+// statistic they need from ALL peers' buffers and add the `world` values themselves, in rank order (bit-identical
+// on every rank).  Hand-shake: after its finalise kernel a rank stamps flag[rank] in every peer's buffer
+// (st.release.sys after a system fence); a consumer block spins (bounded) until all `world` local flags carry the
+// step's stamp (ld.acquire.sys) before its first peer read.  Buffers alternate with the step parity, so a fast rank
+// can never overwrite statistics a slow one is still reading (it cannot get two steps ahead: its next hand-shake
+// needs the slow rank's stamp).
+constexpr int kMaxPeers = 8;
+struct PeerView {
+    const float* stats[kMaxPeers];   // this step's packed statistics of every rank (world == 1: the local buffer)
+    const unsigned* flags;           // local flags [world] (nullptr: no hand-shake)
+    int world;
+    unsigned stamp;
+    int* timeout;                    // set to 1 when the bounded wait expired (peer died): results are then invalid
+};
+struct PeerFlags {
+    unsigned* flags[kMaxPeers];      // flag arrays of every rank (peer-mapped)
+};
+
+__device__ __forceinline__ float peer_sum(const PeerView& pv, size_t e) {
+    float s = __ldcg(pv.stats[0] + e);
+#pragma unroll 1
+    for (int r = 1; r < pv.world; ++r) s += __ldcg(pv.stats[r] + e);
+    return s;
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Block-wide: wait until every rank has published this step's statistics.
+__device__ __forceinline__ void peer_wait(const PeerView& pv) {
+    if (pv.flags == nullptr) return;
+    if ((int)threadIdx.x < pv.world) {
+        const long long t0 = clock64();
+        while ((int)(ld_acquire_sys(pv.flags + threadIdx.x) - pv.stamp) < 0) {
+            if (clock64() - t0 > 4000000000LL) {   // ~2 s at 1.9 GHz: a peer is gone; do not hang the GPU
+                if (pv.timeout) *pv.timeout = 1;
+                break;
+            }
+        }
+    }
+    __syncthreads();
+}
+__global__ void peer_signal_kernel(PeerFlags pf, int world, int rank, unsigned stamp) {
+    if ((int)threadIdx.x < world) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pf.flags[threadIdx.x] + rank), "r"(stamp) : "memory");
+    }
+}
+
 // torch/optim/adam.py (_single_tensor_adam): exp_avg.lerp_(grad, 1 - beta1);
 // exp_avg_sq = beta2 exp_avg_sq + (1 - beta2) grad^2; denom = sqrt(exp_avg_sq) / sqrt(bc2) + eps;
 // param -= (lr / bc1) * exp_avg / denom
@@ -49,7 +103,7 @@ __device__ __forceinline__ float adam_update(float p, float g, float* m, float* 
 __device__ __forceinline__ int low_index(int a, int b) { return a * (a - 1) / 2 + b; }  // torch.tril_indices(D, D, -1) order
 
 // One block per component, D*D threads.  update == 0: only the transform Sigma_j = L_j L_j^T.
-__global__ void sgd_component_kernel(int update, const float* __restrict__ stats, float inv_n, float reg, AdamCfg cfg,
+__global__ void sgd_component_kernel(int update, const PeerView pv, float inv_n, float reg, AdamCfg cfg,
                                      int D, int K, float* __restrict__ means, float* __restrict__ l_diag,
                                      float* __restrict__ l_lower, float* m_mu, float* v_mu, float* m_ld, float* v_ld,
                                      float* m_ll, float* v_ll, float* __restrict__ Sigma) {
@@ -64,9 +118,10 @@ __global__ void sgd_component_kernel(int update, const float* __restrict__ stats
     L[t] = (a == b) ? expf(ld[a]) : (a > b ? ll[low_index(a, b)] : 0.f);
     __syncthreads();
     if (update) {
-        const float* s1 = stats + K + (size_t)j * D;
-        const float* S2 = stats + K + (size_t)K * D + (size_t)j * D * D;
-        float g = -0.5f * inv_n * S2[t];
+        peer_wait(pv);
+        const size_t s1 = (size_t)K + (size_t)j * D;                              // offsets in the packed buffer
+        const size_t S2 = (size_t)K + (size_t)K * D + (size_t)j * D * D;
+        float g = -0.5f * inv_n * peer_sum(pv, S2 + t);
         if (a == b) {
             float sd = 0.f;
             for (int c = 0; c <= a; ++c) sd = fmaf(L[a * D + c], L[a * D + c], sd);   // Sigma_j[a,a]
@@ -92,7 +147,7 @@ __global__ void sgd_component_kernel(int update, const float* __restrict__ stats
         }
         if (b == 0) {
             const int i = j * D + a;
-            means[i] = adam_update(means[i], -inv_n * s1[a], m_mu + i, v_mu + i, cfg);
+            means[i] = adam_update(means[i], -inv_n * peer_sum(pv, s1 + a), m_mu + i, v_mu + i, cfg);
         }
         __syncthreads();
         L[t] = newL;
@@ -106,7 +161,7 @@ __global__ void sgd_component_kernel(int update, const float* __restrict__ stats
 
 // One block of roundup(K) threads: 256, 512 or 1024 (K <= 1024).  update == 0: only log_alpha = log_softmax(soft_weights).
 // epoch_acc (optional, 2 doubles): += (sum_i ll_i of the minibatch, non-PD pair count) from the stats tail.
-__global__ void sgd_weights_kernel(int update, const float* __restrict__ stats, float inv_n, AdamCfg cfg, int D, int K,
+__global__ void sgd_weights_kernel(int update, const PeerView pv, float inv_n, AdamCfg cfg, int D, int K,
                                    float* __restrict__ soft_weights, float* m_sw, float* v_sw,
                                    float* __restrict__ log_alpha, double* epoch_acc) {
     __shared__ float red[1024];
@@ -138,7 +193,8 @@ __global__ void sgd_weights_kernel(int update, const float* __restrict__ stats, 
     };
     float w = t < K ? soft_weights[t] : -INFINITY;
     if (update) {
-        const float s0 = t < K ? stats[t] : 0.f;
+        peer_wait(pv);
+        const float s0 = t < K ? peer_sum(pv, t) : 0.f;
         const float mx = block_max(w);
         const float e = t < K ? expf(w - mx) : 0.f;
         float se, ss;
@@ -150,9 +206,15 @@ __global__ void sgd_weights_kernel(int update, const float* __restrict__ stats, 
             soft_weights[t] = w;
         }
         if (t == 0 && epoch_acc) {
-            const float* tail = stats + (size_t)K * (1 + D + D * D);
-            epoch_acc[0] += (double)tail[0] + (double)tail[1];
-            epoch_acc[1] += (double)tail[3];
+            const size_t tail = (size_t)K * (1 + D + D * D);
+            double ll = 0.0, bad = 0.0;
+            for (int r = 0; r < pv.world; ++r) {
+                ll += (double)__ldcg(pv.stats[r] + tail) + (double)__ldcg(pv.stats[r] + tail + 1);
+                bad += (double)__ldcg(pv.stats[r] + tail + 3);
+            }
+            if (pv.timeout && *pv.timeout) bad += 1.0;     // a peer never answered: poison the epoch like a non-PD pair
+            epoch_acc[0] += ll;
+            epoch_acc[1] += bad;
         }
     }
     const float mx = block_max(w);
@@ -160,6 +222,13 @@ __global__ void sgd_weights_kernel(int update, const float* __restrict__ stats, 
     float se, dummy;
     block_sum2(e, 0.f, se, dummy);
     if (t < K) log_alpha[t] = (w - mx) - logf(se);
+}
+
+inline PeerView local_view(const float* stats) {
+    PeerView pv{};
+    pv.stats[0] = stats;
+    pv.world = 1;
+    return pv;
 }
 
 inline int weights_block(int K) { return K <= 256 ? 256 : (K <= 512 ? 512 : 1024); }
@@ -182,11 +251,39 @@ int dgmm_sgd_params_f32(const float* soft_weights, const float* l_diag, const fl
     cudaStream_t st = (cudaStream_t)stream;
     AdamCfg cfg{};
     sgd_component_kernel<<<K, D * D, 2 * D * D * sizeof(float), st>>>(
-        0, nullptr, 0.f, 0.f, cfg, D, K, nullptr, const_cast<float*>(l_diag), const_cast<float*>(l_lower), nullptr,
+        0, local_view(nullptr), 0.f, 0.f, cfg, D, K, nullptr, const_cast<float*>(l_diag), const_cast<float*>(l_lower), nullptr,
         nullptr, nullptr, nullptr, nullptr, nullptr, Sigma);
     CUDA_TRY(cudaGetLastError());
-    sgd_weights_kernel<<<1, weights_block(K), 0, st>>>(0, nullptr, 0.f, cfg, D, K, const_cast<float*>(soft_weights), nullptr, nullptr,
+    sgd_weights_kernel<<<1, weights_block(K), 0, st>>>(0, local_view(nullptr), 0.f, cfg, D, K, const_cast<float*>(soft_weights), nullptr, nullptr,
                                           log_alpha, nullptr);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+static int adam_launch(const PeerView& pv, double n_batch, double n_total, float w, float lr, float beta1, float beta2,
+                       float eps, int step, int D, int K, float* soft_weights, float* means, float* l_diag,
+                       float* l_lower, float* const* exp_avg, float* const* exp_avg_sq, float* log_alpha, float* Sigma,
+                       double* epoch_acc, cudaStream_t st) {
+    int rc = check_shape(D, K);
+    if (rc) return rc;
+    if (!soft_weights || !means || !l_diag || (D > 1 && !l_lower) || !exp_avg || !exp_avg_sq || !log_alpha ||
+        !Sigma || step < 1 || !(n_batch > 0) || !(n_total > 0))
+        return DGMM_ERR_BAD_ARG;
+    for (int i = 0; i < 4; ++i)
+        if ((i != 3 || D > 1) && (!exp_avg[i] || !exp_avg_sq[i])) return DGMM_ERR_BAD_ARG;
+    AdamCfg cfg;
+    cfg.lr = lr; cfg.beta1 = beta1; cfg.beta2 = beta2; cfg.eps = eps;
+    cfg.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+    cfg.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
+    const float inv_n = (float)(1.0 / n_batch);
+    const float reg = (float)(n_batch / n_total * (double)w);
+    // exp_avg / exp_avg_sq: [0] soft_weights, [1] means, [2] l_diag, [3] l_lower
+    sgd_component_kernel<<<K, D * D, 2 * D * D * sizeof(float), st>>>(1, pv, inv_n, reg, cfg, D, K, means, l_diag,
+                                                                      l_lower, exp_avg[1], exp_avg_sq[1], exp_avg[2],
+                                                                      exp_avg_sq[2], exp_avg[3], exp_avg_sq[3], Sigma);
+    CUDA_TRY(cudaGetLastError());
+    sgd_weights_kernel<<<1, weights_block(K), 0, st>>>(1, pv, inv_n, cfg, D, K, soft_weights, exp_avg[0], exp_avg_sq[0],
+                                                       log_alpha, epoch_acc);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -195,29 +292,40 @@ int dgmm_sgd_adam_step_f32(const float* stats, double n_batch, double n_total, f
                            float beta2, float eps, int step, int D, int K, float* soft_weights, float* means,
                            float* l_diag, float* l_lower, float* const* exp_avg, float* const* exp_avg_sq,
                            float* log_alpha, float* Sigma, double* epoch_acc, void* stream) {
-    int rc = check_shape(D, K);
-    if (rc) return rc;
-    if (!stats || !soft_weights || !means || !l_diag || (D > 1 && !l_lower) || !exp_avg || !exp_avg_sq || !log_alpha ||
-        !Sigma || step < 1 || !(n_batch > 0) || !(n_total > 0))
+    if (!stats) return DGMM_ERR_BAD_ARG;
+    return adam_launch(local_view(stats), n_batch, n_total, w, lr, beta1, beta2, eps, step, D, K, soft_weights, means,
+                       l_diag, l_lower, exp_avg, exp_avg_sq, log_alpha, Sigma, epoch_acc, (cudaStream_t)stream);
+}
+
+// The same step with the cross-GPU SUM of the statistics fused into the Adam kernels (no collective call):
+// peer_bufs[r] = rank r's symmetric buffer as mapped in THIS process; this step's statistics of rank r sit at
+// peer_bufs[r] + stats_off (floats), the hand-shake flags [world] of rank r at peer_bufs[r] + flags_off.  The local
+// statistics must already be in peer_bufs[rank] + stats_off (written by the statistics pass on the same stream).
+// `stamp` must grow by one per step; `timeout_flag` (device int, zero-initialised) reports a peer that never answered.
+int dgmm_sgd_adam_step_peers_f32(void* const* peer_bufs, int world, int rank, int64_t stats_off, int64_t flags_off,
+                                 uint32_t stamp, int* timeout_flag, double n_batch, double n_total, float w, float lr,
+                                 float beta1, float beta2, float eps, int step, int D, int K, float* soft_weights,
+                                 float* means, float* l_diag, float* l_lower, float* const* exp_avg,
+                                 float* const* exp_avg_sq, float* log_alpha, float* Sigma, double* epoch_acc,
+                                 void* stream) {
+    if (!peer_bufs || world < 1 || world > kMaxPeers || rank < 0 || rank >= world || stats_off < 0 || flags_off < 0)
         return DGMM_ERR_BAD_ARG;
-    for (int i = 0; i < 4; ++i)
-        if ((i != 3 || D > 1) && (!exp_avg[i] || !exp_avg_sq[i])) return DGMM_ERR_BAD_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    AdamCfg cfg;
-    cfg.lr = lr; cfg.beta1 = beta1; cfg.beta2 = beta2; cfg.eps = eps;
-    cfg.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
-    cfg.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
-    const float inv_n = (float)(1.0 / n_batch);
-    const float reg = (float)(n_batch / n_total * (double)w);
-    // exp_avg / exp_avg_sq: [0] soft_weights, [1] means, [2] l_diag, [3] l_lower
-    sgd_component_kernel<<<K, D * D, 2 * D * D * sizeof(float), st>>>(1, stats, inv_n, reg, cfg, D, K, means, l_diag,
-                                                                      l_lower, exp_avg[1], exp_avg_sq[1], exp_avg[2],
-                                                                      exp_avg_sq[2], exp_avg[3], exp_avg_sq[3], Sigma);
+    PeerView pv{};
+    PeerFlags pf{};
+    for (int r = 0; r < world; ++r) {
+        if (!peer_bufs[r]) return DGMM_ERR_BAD_ARG;
+        pv.stats[r] = (const float*)peer_bufs[r] + stats_off;
+        pf.flags[r] = (unsigned*)((float*)peer_bufs[r] + flags_off);
+    }
+    pv.flags = pf.flags[rank];
+    pv.world = world;
+    pv.stamp = stamp;
+    pv.timeout = timeout_flag;
+    peer_signal_kernel<<<1, 32, 0, st>>>(pf, world, rank, stamp);
     CUDA_TRY(cudaGetLastError());
-    sgd_weights_kernel<<<1, weights_block(K), 0, st>>>(1, stats, inv_n, cfg, D, K, soft_weights, exp_avg[0], exp_avg_sq[0], log_alpha,
-                                          epoch_acc);
-    CUDA_TRY(cudaGetLastError());
-    return 0;
+    return adam_launch(pv, n_batch, n_total, w, lr, beta1, beta2, eps, step, D, K, soft_weights, means, l_diag, l_lower,
+                       exp_avg, exp_avg_sq, log_alpha, Sigma, epoch_acc, st);
 }
 
 // One minibatch step of BaseSGDGMM.fit as ONE call (the host side of a step is otherwise three ctypes round trips

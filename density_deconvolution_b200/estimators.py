@@ -669,6 +669,33 @@ class BaseSGDGMM:
             states.append(st)
         return params, states
 
+    peer_reduce = True   # distributed fused step: sum the ranks' statistics inside the Adam kernels (NVLink peer memory)
+
+    def _peer_reduce(self):
+        """The symmetric buffer of the fused cross-GPU reduction (created once per estimator; collective).  ``None``
+        when it is switched off (``peer_reduce = False`` / ``DGMM_PEER_REDUCE=0``), the process group is not NCCL, or the
+        ranks do not all get peer access: the step then all-reduces through NCCL (every rank agrees on the choice)."""
+        import os
+        if hasattr(self, "_peers"):
+            return self._peers
+        self._peers = None
+        import torch.distributed as dist
+        want = (self.peer_reduce and os.environ.get("DGMM_PEER_REDUCE", "1") != "0" and hasattr(_ops, "PeerReduce")
+                and dist.get_backend() == "nccl" and _dist.world_size() <= 8)
+        ok = torch.tensor([1 if want else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            return None
+        peers = None
+        try:
+            peers = _ops.PeerReduce(self.d, self.k, self.device)
+        except Exception:  # noqa: BLE001  (no symmetric memory on this box)
+            peers = None
+        ok = torch.tensor([1 if peers is not None else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        self._peers = peers if int(ok.item()) == 1 else None
+        return self._peers
+
     def _fused_epoch(self, loader, n_total, sizes):
         """One epoch of sgd_gmm.py:167-182 on the fused kernels: per minibatch ONE statistics pass
         (forward and backward of the loss), one all-reduce, one Adam step on the ``[K,.]`` parameters
@@ -687,12 +714,16 @@ class BaseSGDGMM:
                                       log_alpha, Sigma, epoch_acc, self.w, group["betas"], group["eps"])
             perm = torch.randperm(loader.n, device=self.device, generator=loader.generator) if loader.shuffle else None
             distributed = _dist.is_distributed()
+            peers = self._peer_reduce() if distributed else None
             bs = loader.batch_size
             for b in range(len(loader)):
                 lo = b * bs
                 nb = min(bs, loader.n - lo)
                 step += 1
-                if distributed:
+                if distributed and peers is not None:
+                    # no collective call: the Adam kernels add the ranks' statistics over NVLink peer memory
+                    stepper.step_peers(perm, lo, nb, sizes[b], n_total, group["lr"], step, peers)
+                elif distributed:
                     stepper.step(perm, lo, nb, 1, sizes[b], n_total, group["lr"], step)
                     _dist.allreduce_stats(stepper.stats)
                     stepper.step(perm, lo, nb, 2, sizes[b], n_total, group["lr"], step)

@@ -507,14 +507,70 @@ class SgdStepper:
         self._fn = _lib.lib().dgmm_sgd_fused_step_f32
         self._stream = _stream(dev)
 
-    def step(self, perm, batch_lo, B, phase, n_batch, n_total, lr, step):
-        """``perm``: int64 CUDA permutation of the table rows (None: contiguous batch)."""
+    def step(self, perm, batch_lo, B, phase, n_batch, n_total, lr, step, stats_ptr=None):
+        """``perm``: int64 CUDA permutation of the table rows (None: contiguous batch).  ``stats_ptr``: device address
+        the packed statistics go to (default: ``self.stats``)."""
         w, b1, b2, eps = self._hyper
+        sp = self._stats_p if stats_ptr is None else ctypes.c_void_p(int(stats_ptr))
         with torch.cuda.device(self.dev):
             rc = self._fn(*self._head, ctypes.c_void_p(perm.data_ptr()) if perm is not None else None, int(batch_lo),
-                          int(B), *self._bufs, int(phase), self._stats_p, float(n_batch), float(n_total), w, float(lr),
+                          int(B), *self._bufs, int(phase), sp, float(n_batch), float(n_total), w, float(lr),
                           b1, b2, eps, int(step), *self._tail, _stream(self.dev))
         check(rc, "dgmm_sgd_fused_step_f32")
+
+    def step_peers(self, perm, batch_lo, B, n_batch, n_total, lr, step, peers):
+        """The distributed step WITHOUT a collective call: statistics into this rank's symmetric buffer, then the Adam
+        kernels add the ``world`` ranks' statistics themselves over NVLink peer memory (``PeerReduce``)."""
+        stamp = peers.next_stamp()          # the buffer's own step counter (every rank advances it in lockstep)
+        off = peers.stats_offset(stamp)
+        self.step(perm, batch_lo, B, 1, n_batch, n_total, lr, step, stats_ptr=peers.local_ptr + 4 * off)
+        w, b1, b2, eps = self._hyper
+        t = self._tail
+        with torch.cuda.device(self.dev):
+            rc = _lib.lib().dgmm_sgd_adam_step_peers_f32(
+                peers.ptr_array, peers.world, peers.rank, off, peers.flags_off, stamp & 0xffffffff,
+                _ptr(peers.timeout), float(n_batch), float(n_total), w, float(lr), b1, b2, eps, int(step), self.D, self.K,
+                t[0], t[1], t[2], t[3], t[4], t[5], t[6], t[7], t[8], _stream(self.dev))
+        check(rc, "dgmm_sgd_adam_step_peers_f32")
+
+
+class PeerReduce:
+    """Symmetric (peer-mapped) buffer for the fused cross-GPU reduction of the SGD step
+    (``dgmm_sgd_adam_step_peers_f32``): two packed-statistics regions (alternating with the step parity) and the
+    hand-shake flags, allocated and exchanged through ``torch.distributed._symmetric_memory`` (plumbing: the
+    allocation and the handle exchange; every access to it is made by this library's kernels).  Collective: every
+    rank of ``group`` must construct it at the same point.  Raises when the box has no peer access."""
+
+    def __init__(self, D, K, device, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if self.world > 8:
+            raise DgmmError("peer reduction is for one NVLink box (world <= 8)")
+        L = stats_len(D, K)
+        self.region = (L + 63) // 64 * 64
+        self.flags_off = 2 * self.region
+        self.buf = symm_mem.empty(2 * self.region + 64, dtype=torch.float32, device=device)
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        self.hdl = symm_mem.rendezvous(self.buf, group)
+        ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        if len(ptrs) != self.world or any(p == 0 for p in ptrs):
+            raise DgmmError("symmetric memory rendezvous returned no peer pointers")
+        self.ptr_array = (ctypes.c_void_p * 8)(*(ptrs + [None] * (8 - self.world)))
+        self.local_ptr = ptrs[self.rank]
+        self.timeout = torch.zeros(1, dtype=torch.int32, device=device)
+        self.stamp = 0
+        dist.barrier(group)
+
+    def next_stamp(self):
+        self.stamp += 1
+        return self.stamp
+
+    def stats_offset(self, stamp):
+        return (int(stamp) & 1) * self.region
 
 
 # -----------------------------------------------------------------------------------------

@@ -333,6 +333,24 @@ DGMM_API int dgmm_sgd_fused_step_f32(const float* X, const float* S, int noise_l
                                      float* Sigma, double* epoch_acc, void* workspace, size_t workspace_bytes,
                                      void* stream);
 
+/* The Adam step of dgmm_sgd_adam_step_f32 with the cross-GPU SUM of the packed statistics FUSED into its kernels
+ * (no collective call between the statistics pass and the update; replaces the all-reduce of SURVEY.md 8e for the
+ * minibatch-SGD step, where a separate 140 KB NCCL all-reduce costs ~10 % of a 1.3 ms step).  One process per GPU
+ * of one NVLink box (world <= 8).  Every rank owns a SYMMETRIC buffer mapped by all peers; peer_bufs[r] (HOST array
+ * of device pointers) is rank r's buffer as mapped in this process.  Layout in floats: this step's packed statistics
+ * at stats_off (callers alternate two regions with the step parity), `world` uint32 hand-shake flags at flags_off.
+ * The local statistics must already be in peer_bufs[rank] + stats_off (same stream).  The call stamps flag[rank] = stamp
+ * in every peer's buffer (release, system scope); the Adam kernels wait (bounded, ~2 s) for all `world` local flags to
+ * reach `stamp` (acquire), then read each statistic from all peers and add them in rank order - bit-identical on
+ * every rank.  stamp must grow by one per step.  timeout_flag (device int, zeroed by the caller) is set when a peer
+ * never answered; epoch_acc[1] is then poisoned like a non-PD pair. */
+DGMM_API int dgmm_sgd_adam_step_peers_f32(void* const* peer_bufs, int world, int rank, int64_t stats_off,
+                                          int64_t flags_off, uint32_t stamp, int* timeout_flag, double n_batch,
+                                          double n_total, float w, float lr, float beta1, float beta2, float eps,
+                                          int step, int D, int K, float* soft_weights, float* means, float* l_diag,
+                                          float* l_lower, float* const* exp_avg, float* const* exp_avg_sq,
+                                          float* log_alpha, float* Sigma, double* epoch_acc, void* stream);
+
 /* ---- diagnostics (not part of the drop-in surface) ----------------------------------- */
 
 /* Overrides the automatic launch plan of the pair kernel; -1 = automatic for that field.

@@ -45,14 +45,20 @@ def _worker(rank, world, port, payload, out_path):
     m.fit((X[lo:hi].contiguous(), S[lo:hi].contiguous()), init=False)
     res["em_means"], res["em_covars"], res["em_weights"] = (t.cpu().numpy() for t in (m.means, m.covars, m.weights))
     res["em_ll"] = np.asarray(m.log_prob_curve)
-    sg = SGDDeconvGMM(K, D, epochs=2, batch_size=64, lr=1e-2, w=1e-3, device=dev)
-    sg.shuffle = False
-    with torch.no_grad():
-        sg.module.soft_weights.copy_(la)
-        sg.module.means.copy_(mu)
-    sg.fit((X[lo:hi].contiguous(), S[lo:hi].contiguous()), init=False)
-    res["sgd_means"] = sg.means.cpu().numpy()
-    res["sgd_curve"] = np.asarray(sg.train_loss_curve)
+    for tag, peer in (("sgd", True), ("sgd_nccl", False)):
+        # peer = True: the ranks' statistics are summed inside the Adam kernels over NVLink peer memory
+        # (dgmm_sgd_adam_step_peers_f32); False: the NCCL all-reduce between the two phases of the step
+        sg = SGDDeconvGMM(K, D, epochs=2, batch_size=64, lr=1e-2, w=1e-3, device=dev)
+        sg.shuffle = False
+        sg.peer_reduce = peer
+        with torch.no_grad():
+            sg.module.soft_weights.copy_(la)
+            sg.module.means.copy_(mu)
+        sg.fit((X[lo:hi].contiguous(), S[lo:hi].contiguous()), init=False)
+        res[tag + "_means"] = sg.means.cpu().numpy()
+        res[tag + "_covars"] = sg.covars.cpu().numpy()
+        res[tag + "_curve"] = np.asarray(sg.train_loss_curve)
+        res[tag + "_used_peers"] = np.asarray(getattr(sg, "_peers", None) is not None)
     if rank == 0:
         np.savez(out_path, **res)
     dist.barrier()
@@ -102,3 +108,8 @@ def test_two_rank_nccl_statistics_and_fits_equal_single_gpu(tmp_path):
     sg.fit((tX[order].contiguous(), tS[order].contiguous()), init=False)
     ref = sg.means.cpu().numpy()
     assert np.max(np.abs(z["sgd_means"] - ref)) <= 2e-3 * np.max(np.abs(ref))
+    # fused peer-memory reduction == NCCL all-reduce (two ranks: a + b in either order is the same float)
+    assert bool(z["sgd_used_peers"]) and not bool(z["sgd_nccl_used_peers"])
+    np.testing.assert_allclose(z["sgd_curve"], z["sgd_nccl_curve"], rtol=1e-7)
+    assert np.max(np.abs(z["sgd_means"] - z["sgd_nccl_means"])) <= 1e-6 * np.max(np.abs(ref))
+    assert np.max(np.abs(z["sgd_covars"] - z["sgd_nccl_covars"])) <= 1e-6 * np.max(np.abs(z["sgd_nccl_covars"]))
