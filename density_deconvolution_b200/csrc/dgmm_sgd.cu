@@ -56,10 +56,15 @@ struct PeerFlags {
     unsigned* flags[kMaxPeers];      // flag arrays of every rank (peer-mapped)
 };
 
+// All `world` remote loads are issued before the first add (a rank-by-rank loop would pay the NVLink round trip
+// eight times in a row); the sum itself is taken in rank order.
 __device__ __forceinline__ float peer_sum(const PeerView& pv, size_t e) {
-    float s = __ldcg(pv.stats[0] + e);
-#pragma unroll 1
-    for (int r = 1; r < pv.world; ++r) s += __ldcg(pv.stats[r] + e);
+    float v[kMaxPeers];
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r) v[r] = (r < pv.world) ? __ldcg(pv.stats[r] + e) : 0.f;
+    float s = v[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r) s += v[r];
     return s;
 }
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
@@ -121,6 +126,7 @@ __global__ void sgd_component_kernel(int update, const PeerView pv, float inv_n,
         peer_wait(pv);
         const size_t s1 = (size_t)K + (size_t)j * D;                              // offsets in the packed buffer
         const size_t S2 = (size_t)K + (size_t)K * D + (size_t)j * D * D;
+        const float s1_a = (b == 0) ? peer_sum(pv, s1 + a) : 0.f;                 // (both remote reads up front)
         float g = -0.5f * inv_n * peer_sum(pv, S2 + t);
         if (a == b) {
             float sd = 0.f;
@@ -147,7 +153,7 @@ __global__ void sgd_component_kernel(int update, const PeerView pv, float inv_n,
         }
         if (b == 0) {
             const int i = j * D + a;
-            means[i] = adam_update(means[i], -inv_n * peer_sum(pv, s1 + a), m_mu + i, v_mu + i, cfg);
+            means[i] = adam_update(means[i], -inv_n * s1_a, m_mu + i, v_mu + i, cfg);
         }
         __syncthreads();
         L[t] = newL;
@@ -195,6 +201,13 @@ __global__ void sgd_weights_kernel(int update, const PeerView pv, float inv_n, A
     if (update) {
         peer_wait(pv);
         const float s0 = t < K ? peer_sum(pv, t) : 0.f;
+        // tails of the ranks' buffers: lane r reads rank r's (sum ll, non-PD count) in parallel
+        __shared__ double tail_ll[kMaxPeers], tail_bad[kMaxPeers];
+        if (epoch_acc && t < pv.world) {
+            const float* tl = pv.stats[t] + (size_t)K * (1 + D + D * D);
+            tail_ll[t] = (double)__ldcg(tl) + (double)__ldcg(tl + 1);
+            tail_bad[t] = (double)__ldcg(tl + 3);
+        }
         const float mx = block_max(w);
         const float e = t < K ? expf(w - mx) : 0.f;
         float se, ss;
@@ -206,12 +219,8 @@ __global__ void sgd_weights_kernel(int update, const PeerView pv, float inv_n, A
             soft_weights[t] = w;
         }
         if (t == 0 && epoch_acc) {
-            const size_t tail = (size_t)K * (1 + D + D * D);
             double ll = 0.0, bad = 0.0;
-            for (int r = 0; r < pv.world; ++r) {
-                ll += (double)__ldcg(pv.stats[r] + tail) + (double)__ldcg(pv.stats[r] + tail + 1);
-                bad += (double)__ldcg(pv.stats[r] + tail + 3);
-            }
+            for (int r = 0; r < pv.world; ++r) { ll += tail_ll[r]; bad += tail_bad[r]; }
             if (pv.timeout && *pv.timeout) bad += 1.0;     // a peer never answered: poison the epoch like a non-PD pair
             epoch_acc[0] += ll;
             epoch_acc[1] += bad;

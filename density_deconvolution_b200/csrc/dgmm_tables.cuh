@@ -30,11 +30,11 @@ inline PairVariant pair_variant() {
     return v;
 }
 
-// D = 17..DGMM_PAIR_UNROLL_D: the fully unrolled body still fits 255 registers with a few spilled words
+// D = 17..DGMM_PAIR_UNROLL_D (= 20): the fully unrolled body still fits 255 registers with a few spilled words
 // (ptxas: <= 480 bytes of stack at D = 20), which is an order of magnitude faster than the rolled fallback.
 // Compiled only for the group class of K = 64..128 (one block of 128 threads per SM) to keep build time down.
 #ifndef DGMM_PAIR_UNROLL_D
-#define DGMM_PAIR_UNROLL_D 24
+#define DGMM_PAIR_UNROLL_D 20   // (21..24 existed in round 1: 0.10-0.34 of peak; the cooperative kernels serve them now)
 #endif
 template <int D, int MODE, int SIGP, int ACCP, int GCLS, int NZ>
 inline PairVariant pair_variant_wide_unrolled() {

@@ -117,3 +117,62 @@ def test_shard_bounds_cover_everything():
             assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
             sizes = [hi - lo for lo, hi in edges]
             assert max(sizes) - min(sizes) <= 1
+
+
+# ---- unequal shards: the ranks' own batch counts differ (one rank blocked forever in all_reduce) ----------
+def _worker_unequal(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, HERE)
+    torch.set_num_threads(1)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    from density_deconvolution_b200 import estimators as est
+    from density_deconvolution_b200 import util
+    from density_deconvolution_b200.data import DeviceBatches
+    from density_deconvolution_b200.dist import shard_bounds
+    import fake_ops
+    est._ops = fake_ops
+    util._real_ops = fake_ops
+    from helpers import synth
+    rng = np.random.default_rng(78)
+    X, S, alpha, mu, Sigma = synth(rng, 51, 3, 4)          # 26 + 25 points: 3 vs 2 full batches of 10 (+ a tail each)
+    f = lambda a: torch.tensor(a, dtype=torch.float32)  # noqa: E731
+    X, S, alpha, mu, Sigma = f(X), f(S), f(alpha), f(mu), f(Sigma)
+    lo, hi = shard_bounds(X.shape[0])
+    dev = torch.device("cpu")
+    Xs, Ss = X[lo:hi], S[lo:hi]
+    loader = DeviceBatches((Xs[:21 + 5 * (1 - rank)], Ss[:21 + 5 * (1 - rank)]), 10, dev).sync_ranks()   # 26 vs 21 points: 3 vs 3; then
+    n_batches = len(loader)
+    loader2 = DeviceBatches((Xs[:25 - 10 * rank], Ss[:25 - 10 * rank]), 10, dev, drop_last=True).sync_ranks()   # 25 vs 15: 2 vs 1
+    sizes = est._global_batch_sizes(DeviceBatches((Xs, Ss), 10, dev).sync_ranks())
+    s = est.SGDDeconvGMM(4, 3, epochs=2, lr=1e-2, batch_size=10, w=1e-3, k_means_iters=2, device=dev)
+    s.fit((Xs, Ss))                                         # would dead-lock without the rank-synchronised batch count
+    o = est.OnlineDeconvGMM(4, 3, epochs=2, w=1e-3, batch_size=12, step_size=0.2, k_means_iters=2, device=dev)
+    o.fit((Xs, Ss))                                         # drop_last: 2 vs 2 here; init loader 1200-point batches: 1 vs 1
+    q.put((rank, dict(n_batches=n_batches, n_drop=len(loader2), sizes=sizes, n_local=hi - lo,
+                      loss=np.asarray(s.train_loss_curve), means=s.means.numpy(), on_ll=np.asarray(o.train_ll_curve))))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_unequal_shards_do_not_deadlock_and_scale_the_loss_by_the_global_batch():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_unequal, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=240) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got[0]["n_local"] == 26 and got[1]["n_local"] == 25
+    assert got[0]["n_batches"] == got[1]["n_batches"] == 3
+    assert got[0]["n_drop"] == got[1]["n_drop"] == 1            # minimum over ranks of (2, 1)
+    # 26 + 25 points in batches of 10 per rank: global batches 20, 20, 6 + 5
+    assert got[0]["sizes"] == got[1]["sizes"] == [20, 20, 11]
+    np.testing.assert_array_equal(got[0]["loss"], got[1]["loss"])
+    np.testing.assert_array_equal(got[0]["means"], got[1]["means"])
+    np.testing.assert_array_equal(got[0]["on_ll"], got[1]["on_ll"])
+    assert np.all(np.isfinite(got[0]["loss"]))
