@@ -17,6 +17,7 @@ Workloads (per GPU; weak scaling, every rank generates its own shard on the devi
   c2    synthetic N=1e7, D=10, K=64 full noise (configs[1])
   c3    wine table (6497x9, tests/golden) tiled to N=1.25e7 with fresh per-point noise, K=128 (configs[2])
   c4    ionosphere table (351x32, tests/golden) tiled x1024 with fresh per-point noise, K=256 (configs[3])
+  gaia  synthetic N=1.25e7, D=7, K=512 (the reference's Gaia runs; not in BASELINE.json; not a default secondary block)
   small N=1e6, D=10, K=64 (quick check)
 The workloads named by --secondary are measured after the headline one (fewer steps, no end-to-end arm)
 and reported under ``secondary`` in the same JSON line, each with its own roofline block.
@@ -44,6 +45,9 @@ WORKLOADS = {
                name="wine table (6497x9) tiled to N=1.25e7/GPU, fresh per-point full noise, K=128 (configs[2])"),
     "c4": dict(N=351 * 1024, D=32, K=256, noise="full", table="ref_ionosphere_k256_f64.npz", table_iter=5,
                name="ionosphere table (351x32) tiled x1024 per GPU, fresh per-point full noise, K=256 (configs[3])"),
+    "gaia": dict(N=12_500_000, D=7, K=512, noise="full",
+                 name="synthetic N=1.25e7/GPU D=7 K=512 full noise (the shape of the reference's Gaia runs, "
+                      "experiments/gmm/gaia/variable_n/fit_sgd.sh:15)"),
     "small": dict(N=1_000_000, D=10, K=64, noise="full", name="synthetic N=1e6/GPU D=10 K=64 full noise"),
 }
 METRIC = "pair_loglik_evals_per_sec"

@@ -106,8 +106,7 @@ inline int ns_of(int D) { return 1 + D + nd_of(D); }
 
 // Upper bound of the grid used for (D, K): shared by the workspace query and the launcher.
 inline int max_grid(int D, int K, int sms) {
-    (void)K;
-    const size_t per_block = (size_t)ns_of(D) * kPairMaxThreads * 4;  // a column per thread, worst case
+    const size_t per_block = (size_t)ns_of(D) * std::max(kPairMaxThreads, group_size(K)) * 4;  // a column per thread, worst case
     size_t cap = ((size_t)256 << 20) / per_block;
     size_t g = (size_t)sms * 8;
     if (g > cap) g = cap;
@@ -141,7 +140,7 @@ Workspace carve(void* base, int D, int K, int sms) {
     const int mg = max_grid(D, K, sms);
     // (the cooperative path keeps the partial sums of its two passes side by side)
     w.part_ll = (double*)(b + off); off += up256((size_t)mg * (D > 16 ? 4 : 2) * 8);
-    w.part = (float*)(b + off);     off += up256((size_t)mg * ns_of(D) * kPairMaxThreads * 4);
+    w.part = (float*)(b + off);     off += up256((size_t)mg * ns_of(D) * std::max(kPairMaxThreads, GS) * 4);
     w.team_sig = w.team_mu = w.team_cj = nullptr;
     if (D > 16) {
         const size_t Kp = (size_t)K + team::kMaxTB;
@@ -452,7 +451,7 @@ size_t pair_smem_bytes(int D, int noise, bool has_g, int sigp, int accp, int GS,
 inline int group_class(int GS) {
     if (GS < 32) return GCLS_SUB;
     if (GS == 32) return GCLS_WARP;
-    return GS <= 128 ? GCLS_MW4 : GCLS_MWN;
+    return GS <= 128 ? GCLS_MW4 : (GS <= kPairMaxThreads ? GCLS_MWN : GCLS_MWN512);
 }
 
 // Tile geometry for one variant; returns false when it cannot be made to fit.
@@ -968,14 +967,16 @@ int stats_pass_1(const float* X, const float* S, int noise, int64_t N, int D, in
 // Cost: one extra log-likelihood pass (F_ll / F_em = 1/3 more flops than a single-launch E-step).  A
 // responsibility floor (Online EM's 10 eps) is applied as g_c[i] * floor, i.e. scaled by the chunk's share.
 // Scratch: (n_chunks + 1) N floats from the stream-ordered allocator (the only allocation the library makes
-// on the device-pointer API, and only for K > 256).
-constexpr int kChunkK = 256;
+// on the device-pointer API, and only for chunked mixtures).  D <= 8 runs K <= 512 as ONE launch of 512-thread
+// groups (dgmm_tables.cuh: pair_wide512) and chunks above that.
+inline int single_launch_k(int D) { return D <= kPairWideMaxD ? kPairWideThreads : kPairMaxThreads; }
 struct KChunks {
     int n, Kc;
 };
-inline KChunks k_chunks(int K) {
+inline KChunks k_chunks(int K, int D) {
     KChunks c;
-    c.n = (K + kChunkK - 1) / kChunkK;
+    const int cap = single_launch_k(D);
+    c.n = (K + cap - 1) / cap;
     c.Kc = (((K + c.n - 1) / c.n) + 31) & ~31;
     return c;
 }
@@ -1098,7 +1099,7 @@ __global__ void chunk_tail_kernel(const double* __restrict__ part, int nblk, con
 int chunked_loglik(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
                    const float* mu, const float* Sigma, const float* g, float* out_ll, int want_w, float* llc,
                    const ChunkSpace& cs, void* inner_ws, size_t inner_bytes, cudaStream_t st, int* nblk) {
-    const KChunks kc = k_chunks(K);
+    const KChunks kc = k_chunks(K, D);
     for (int c = 0; c < kc.n; ++c) {
         const int c0 = c * kc.Kc, k = std::min(kc.Kc, K - c0);
         Workspace ws;
@@ -1119,13 +1120,13 @@ int chunked_loglik(const float* X, const float* S, int noise, int64_t N, int D, 
 int loglik_pass(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
                 const float* mu, const float* Sigma, float* out_ll, void* workspace, size_t workspace_bytes,
                 cudaStream_t st, Workspace* ws_out, int* nblk) {
-    if (K <= kChunkK)
+    if (K <= single_launch_k(D))
         return loglik_pass_1(X, S, noise, N, D, K, log_alpha, mu, Sigma, out_ll, workspace, workspace_bytes, st, ws_out, nblk);
     DeviceInfo dev;
     int rc = device_info(&dev);
     if (rc) return rc;
     if (!workspace) return DGMM_ERR_WORKSPACE;
-    const KChunks kc = k_chunks(K);
+    const KChunks kc = k_chunks(K, D);
     const size_t inner_bytes = carve(nullptr, D, kc.Kc, dev.sms).bytes;
     const ChunkSpace cs = chunk_space(workspace, D, kc.Kc, inner_bytes);
     if (cs.bytes > workspace_bytes) return DGMM_ERR_WORKSPACE;
@@ -1146,14 +1147,14 @@ int loglik_pass(const float* X, const float* S, int noise, int64_t N, int D, int
 int stats_pass(const float* X, const float* S, int noise, int64_t N, int D, int K, const float* log_alpha,
                const float* mu, const float* Sigma, const float* g, float resp_floor, float* out_ll, float* out_stats,
                int beta, void* workspace, size_t workspace_bytes, cudaStream_t st) {
-    if (K <= kChunkK)
+    if (K <= single_launch_k(D))
         return stats_pass_1(X, S, noise, N, D, K, log_alpha, mu, Sigma, g, resp_floor, out_ll, out_stats, beta, workspace,
                             workspace_bytes, st);
     DeviceInfo dev;
     int rc = device_info(&dev);
     if (rc) return rc;
     if (!workspace) return DGMM_ERR_WORKSPACE;
-    const KChunks kc = k_chunks(K);
+    const KChunks kc = k_chunks(K, D);
     const size_t inner_bytes = carve(nullptr, D, kc.Kc, dev.sms).bytes;
     const ChunkSpace cs = chunk_space(workspace, D, kc.Kc, inner_bytes);
     if (cs.bytes > workspace_bytes) return DGMM_ERR_WORKSPACE;
@@ -1199,8 +1200,8 @@ size_t dgmm_workspace_bytes(int D, int K) {
     if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return 0;
     DeviceInfo dev;
     if (device_info(&dev)) return 0;
-    if (K > kChunkK) {
-        const KChunks kc = k_chunks(K);
+    if (K > single_launch_k(D)) {
+        const KChunks kc = k_chunks(K, D);
         return chunk_space(nullptr, D, kc.Kc, carve(nullptr, D, kc.Kc, dev.sms).bytes).bytes;
     }
     return carve(nullptr, D, K, dev.sms).bytes;
@@ -1208,7 +1209,7 @@ size_t dgmm_workspace_bytes(int D, int K) {
 
 int dgmm_stats_needs_ll(int D, int K, int noise_layout) {
     if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return 0;
-    if (K > kChunkK) return 0;    // the chunked path carries ll_i in its own scratch
+    if (K > single_launch_k(D)) return 0;    // the chunked path carries ll_i in its own scratch
     return use_team_path(D, K, MODE_STATS, noise_layout) ? 1 : 0;
 }
 
@@ -1247,7 +1248,7 @@ int dgmm_debug_get_plan(int mode, int D, int K, int64_t N, int noise, int has_g,
     int rc = device_info(&dev);
     if (rc) return rc;
     if (D < 1 || D > DGMM_MAX_D || K < 1 || K > DGMM_MAX_K) return DGMM_ERR_BAD_ARG;
-    if (K > kChunkK) K = k_chunks(K).Kc;      // component chunks: the plan of one chunk launch
+    if (K > single_launch_k(D)) K = k_chunks(K, D).Kc;      // component chunks: the plan of one chunk launch
     if (use_team_path(D, K, mode, noise)) {
         // cooperative path: sigp = 3 marks it; GS = teams per block, NSLOT = component chunks
         TeamPlan t;

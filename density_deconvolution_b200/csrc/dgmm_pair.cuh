@@ -42,7 +42,9 @@ enum : int { ST_REG = 0, ST_SMEM = 1, ST_GLOBAL = 2, ST_TMEM = 3 };  // where Si
 enum : int { NOISE_FULL = 0, NOISE_DIAG = 1, NOISE_NONE = 2, NOISE_SHARED = 3, NOISE_PACKED = 4 };
 
 constexpr int kMaxStages = 4;
-constexpr int kPairMaxThreads = 256;  // largest block the pair kernel is compiled for
+constexpr int kPairMaxThreads = 256;  // largest block the pair kernel is compiled for (D <= 8 also has 512-thread variants)
+constexpr int kPairWideThreads = 512;
+constexpr int kPairWideMaxD = 8;      // up to here K = 257..512 runs as ONE group of 512 threads (<= 128 registers each)
 constexpr int kSmemHeader = 1152;  // mbarriers (64 B) + logsumexp exchange (2 x 256 B) + double reduce (512 B)
 
 struct PairParams {
@@ -165,7 +167,8 @@ __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // group classes of the pair kernel (see dgmm_pair_body.inc)
-enum : int { GCLS_SUB = 0, GCLS_WARP = 1, GCLS_MW4 = 2, GCLS_MWN = 3, GCLS_ANY = 4 };
+enum : int { GCLS_SUB = 0, GCLS_WARP = 1, GCLS_MW4 = 2, GCLS_MWN = 3, GCLS_ANY = 4,
+             GCLS_MWN512 = 5 };   // host-side only: GCLS_MWN compiled for blocks of 512 threads (GS = 257..512, D <= 8)
 // noise classes of the pair kernel
 enum : int { NZ_FULL = 0, NZ_DIAG = 1, NZ_ANY = 2, NZ_PACKED = 3 };
 

@@ -91,8 +91,25 @@ inline PairVariant pair_by_gcls(int gcls, int nz) {
 //   D = 17..24   : K >= 64: as 13..16 (unrolled, a few spilled words; Sigma_j through L1 when its columns
 //                  would leave one block per SM, and for K > 128); otherwise the fallback
 //   D = 21..32, and D = 17..20 with K < 64: the cooperative 8-lane-team kernels (dgmm_team.cuh)
+// K = 257..512 at D <= 8 (the reference's Gaia runs: D = 7, K = 512): one group of 512 threads, i.e. the whole mixture in
+// ONE launch (no component chunks, no second pass): Sigma_j in shared-memory columns, accumulators in tensor memory.
+template <int D, int MODE, int ACCP>
+inline PairVariant pair_wide512(int nz) {
+    if (nz == NZ_FULL) return pair_variant<D, MODE, ST_SMEM, ACCP, GCLS_MWN, NZ_FULL, kPairWideThreads, 1>();
+    if (nz == NZ_PACKED) return pair_variant<D, MODE, ST_SMEM, ACCP, GCLS_MWN, NZ_PACKED, kPairWideThreads, 1>();
+    return pair_variant<D, MODE, ST_SMEM, ACCP, GCLS_MWN, NZ_DIAG, kPairWideThreads, 1>();
+}
+
 template <int D>
 inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
+    if (gcls == GCLS_MWN512) {
+        if constexpr (D <= kPairWideMaxD) {
+            if (which != 0) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
+            if (mode == MODE_LOGLIK) return pair_wide512<D, MODE_LOGLIK, ST_GLOBAL>(nz);
+            return pair_wide512<D, MODE_STATS, ST_TMEM>(nz);
+        }
+        return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
+    }
     if (which == 2) {
         // universal fallback of the thread-per-pair family; above D = 16 the cooperative kernels
         // (dgmm_team.cuh) serve everything the unrolled variants do not

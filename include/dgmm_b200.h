@@ -43,7 +43,7 @@ extern "C" {
 
 #define DGMM_ABI_VERSION 2
 #define DGMM_MAX_D 32
-#define DGMM_MAX_K 1024 /* one launch serves 256 components; larger K runs in component chunks (see dgmm_estep_stats_f32) */
+#define DGMM_MAX_K 1024 /* one launch serves 256 components (512 for D <= 8); larger K runs in component chunks (see dgmm_estep_stats_f32) */
 
 /* error codes (negative) */
 #define DGMM_OK 0
@@ -110,8 +110,8 @@ DGMM_API int dgmm_loglik_f32(const float* X, const float* S, int noise_layout, i
  * Replaces deconv/gmm/deconv_gmm.py:39-107 (E-step + the reductions of the M-step),
  * deconv/gmm/batch_deconv_gmm.py:95-120, deconv/gmm/online_deconv_gmm.py:148-166 and the
  * autograd backward of deconv/gmm/sgd_deconv_gmm.py:14-28 (deconv/gmm/sgd_gmm.py:181).
- * K > 256 (the reference's Gaia runs use K = 512, experiments/gmm/gaia/variable_k/fit_em.sh:18): the components
- * are served in chunks of <= 256 - a log-likelihood pass per chunk, ll_i = logsumexp over the chunks, then a
+ * K > 256 (the reference's Gaia runs use D = 7, K = 512, experiments/gmm/gaia/variable_k/fit_em.sh:18): D <= 8 serves
+ * K <= 512 in one launch of 512-thread groups; otherwise the components are served in chunks of <= 256 (<= 512) - a log-likelihood pass per chunk, ll_i = logsumexp over the chunks, then a
  * statistics pass per chunk weighted with g_i exp(ll_chunk,i - ll_i), which makes omega_ij exact; a non-zero
  * resp_floor is scaled by the chunk's share of the point.
  *   g [N] optional per-point weights (NULL = 1; = grad_output for the SGD backward);

@@ -141,11 +141,22 @@ def test_component_chunks(ops, D, K):
     run_case(ops, N=N, D=D, K=K, seed=8000 + D + K, with_g=(K % 2 == 0))
 
 
+def test_wide_groups_are_one_launch_up_to_d8(ops):
+    """D <= 8 serves K = 257..512 as ONE group of 512 threads (the Gaia shape D = 7, K = 512); larger D or K chunk."""
+    assert ops.get_plan(1, 7, 512, 100000)["GS"] == 512 and ops.get_plan(1, 7, 512, 100000)["TPB"] == 512
+    assert ops.get_plan(0, 8, 300, 100000)["GS"] == 320
+    assert ops.get_plan(1, 9, 512, 100000)["GS"] == 256          # two chunks of 256
+    assert ops.get_plan(1, 7, 1024, 100000)["GS"] == 512         # two chunks of 512
+    for D, K, noise in ((7, 512, "full"), (8, 400, "packed"), (5, 290, "diag"), (1, 512, "full"), (7, 1024, "full")):
+        run_case(ops, N=70, D=D, K=K, seed=8050 + D + K, noise=noise, with_g=True)
+    run_case(ops, N=40, D=6, K=480, seed=8060, floor=10 * float(np.finfo(np.float32).eps))   # exact floor: one launch
+
+
 def test_component_chunks_noise_layouts_and_floor(ops):
-    run_case(ops, N=90, D=5, K=300, seed=8100, noise="diag")
-    run_case(ops, N=90, D=6, K=300, seed=8101, noise="packed")
+    run_case(ops, N=90, D=9, K=300, seed=8100, noise="diag")
+    run_case(ops, N=90, D=10, K=300, seed=8101, noise="packed")
     # a responsibility floor is scaled by the chunk's share of each point: bounded deviation, documented
-    D, K, N, floor = 4, 320, 120, 10 * np.finfo(np.float32).eps
+    D, K, N, floor = 9, 320, 120, 10 * np.finfo(np.float32).eps
     rng = np.random.default_rng(8102)
     X, S, alpha, mu, Sigma = synth(rng, N, D, K)
     tX, tS, tmu, tSg = to_dev(X, S, mu, Sigma)
@@ -160,7 +171,7 @@ def test_component_chunks_noise_layouts_and_floor(ops):
 def test_component_chunks_em_fit_and_full(ops):
     """EM iterations and the materialising E-step at K = 300 track the oracle."""
     from density_deconvolution_b200 import DeconvGMM
-    D, K, N = 3, 300, 900
+    D, K, N = 9, 300, 900
     rng = np.random.default_rng(8200)
     X, S, alpha, mu, Sigma = synth(rng, N, D, K)
     m = DeconvGMM(K, D, epochs=2, w=1e-3, tol=0.0, device=dev())
@@ -181,7 +192,7 @@ def test_component_chunks_em_fit_and_full(ops):
 
 
 def test_nonpd_is_reported_through_chunks(ops):
-    D, K, N = 3, 300, 20
+    D, K, N = 9, 300, 20
     rng = np.random.default_rng(8300)
     X, S, alpha, mu, Sigma = synth(rng, N, D, K)
     Sigma = Sigma.copy()
