@@ -410,8 +410,12 @@ __global__ void __launch_bounds__(256, 2) team_loglik_kernel(const TeamParams p)
 // ---------------------------------------------------------------------------------------------------
 // statistics pass
 // ---------------------------------------------------------------------------------------------------
+// Register cap of the statistics pass: two blocks per SM at 128 registers up to D = 26; from D = 27 the 80+ matrix
+// registers per lane spill at that cap (4.3e8 local loads per launch at D = 32) and ONE block at 255 registers is
+// faster (gpurun A/B, N = 262 144: D=32,K=256 179.8 -> 164.6 ms; D=28,K=128 74.0 -> 71.5; D=24,K=128 42.7 -> 46.4).
+constexpr int team_stats_min_blocks(int D) { return D >= 27 ? 1 : 2; }
 template <int D, int NZ>
-__global__ void __launch_bounds__(256, 2) team_stats_kernel(const TeamParams p) {
+__global__ void __launch_bounds__(256, team_stats_min_blocks(D)) team_stats_kernel(const TeamParams p) {
     using G = Geo<D>;
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, TPB = blockDim.x;
