@@ -330,6 +330,7 @@ class Env:
 def measure(env, args, key, wl, N, steps, warmup, do_sgd, do_e2e):
     """EM iteration, log-likelihood pass, SGD step (and the end-to-end arm) of one workload."""
     import torch
+    from density_deconvolution_b200.dist import allreduce_stats
     ops, dist, dev, world, rank = env.ops, env.dist, env.dev, env.world, env.rank
     D, K = wl["D"], wl["K"]
     X, S, alpha, mu0, Sigma0, data_kind = make_workload(wl, N, dev, rank)
@@ -346,7 +347,7 @@ def measure(env, args, key, wl, N, steps, warmup, do_sgd, do_e2e):
         a, la, m, Sg = p
         ops.estep_stats(X, S, la, m, Sg, noise=wl["noise"], want_ll=False, out_stats=stats)
         if world > 1:
-            dist.all_reduce(stats)
+            allreduce_stats(stats)       # (the double sum of the log-likelihoods is reduced as a double)
         ops.mstep_update(stats, n_total, w_reg, m, Sg, a, la)
 
     def ll_step(p):
@@ -442,6 +443,7 @@ def measure(env, args, key, wl, N, steps, warmup, do_sgd, do_e2e):
 
 
 def run_packed(env, wl, X, S, fresh, n_total, w_reg, steps, timed):
+    from density_deconvolution_b200.dist import allreduce_stats
     """The same EM iteration and log-likelihood pass with the noise table in the PACKED lower-triangular layout
     ``[N, D(D+1)/2]`` (DGMM_NOISE_PACKED): 1.7-1.9x fewer input bytes, same arithmetic."""
     import torch
@@ -458,7 +460,7 @@ def run_packed(env, wl, X, S, fresh, n_total, w_reg, steps, timed):
         a, la, m, Sg = p
         ops.estep_stats(X, P, la, m, Sg, noise="packed", want_ll=False, out_stats=stats)
         if world > 1:
-            dist.all_reduce(stats)
+            allreduce_stats(stats)       # (the double sum of the log-likelihoods is reduced as a double)
         ops.mstep_update(stats, n_total, w_reg, m, Sg, a, la)
 
     def ll_step(p):
@@ -689,6 +691,7 @@ def run_e2e(args, env, wl, X, S, fresh, n_total, w_reg, steps):
     the log-likelihood back (D2H).  The pinned copy of the shard is bounded by the host memory that is
     free (a third of MemAvailable shared by the ranks): a prefix of the shard is streamed when it does not fit."""
     import torch
+    from density_deconvolution_b200.dist import allreduce_stats
     ops, dist, dev, world = env.ops, env.dist, env.dev, env.world
     N, D = X.shape
     K = wl["K"]
@@ -717,7 +720,7 @@ def run_e2e(args, env, wl, X, S, fresh, n_total, w_reg, steps):
             return c.em_iteration(hX, hS_, w_reg, ha, hm, hSg, noise=noise)[0]
         c.estep_stats(hX, hS_, ha, hm, hSg, noise=noise, out=h_stats)
         d_stats.copy_(h_stats, non_blocking=True)
-        dist.all_reduce(d_stats)
+        allreduce_stats(d_stats)
         d_par[2].copy_(hm)
         d_par[3].copy_(hSg)
         ops.mstep_update(d_stats, n_e2e_total, w_reg, d_par[2], d_par[3], d_par[0], d_par[1])

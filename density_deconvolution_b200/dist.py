@@ -29,10 +29,17 @@ def shard_bounds(n, r=None, ws=None):
 
 
 def allreduce_stats(stats):
-    """In-place SUM of the packed statistics across ranks (no-op for one process).
-    Every slot of the buffer is additive, including the (ll_hi, ll_lo) float pair."""
+    """In-place SUM of the packed statistics across ranks (no-op for one process).  Every slot of the buffer is
+    additive; the ``(ll_hi, ll_lo)`` float pair that carries the DOUBLE ``sum_i ll_i`` is reduced as a double of its
+    own (a float32 sum of the ``hi`` parts would round the total to ~1e-7 relative, which at ``|ll| ~ 1e9`` is hundreds
+    of units - enough to fake or hide the ``|ll - prev| < tol`` convergence test) and split again afterwards."""
     if is_distributed():
+        tail = (stats[-4].double() + stats[-3].double()).reshape(1)
         dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+        dist.all_reduce(tail, op=dist.ReduceOp.SUM)
+        hi = tail.to(torch.float32)
+        stats[-4:-3] = hi
+        stats[-3:-2] = torch.where(torch.isfinite(hi), (tail - hi.double()).to(torch.float32), torch.zeros_like(hi))
     return stats
 
 

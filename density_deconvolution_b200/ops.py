@@ -47,6 +47,14 @@ def workspace(D, K, device):
     return ws
 
 
+def clear_workspaces():
+    """Drops the cached per-(D, K, device) workspaces and scratch vectors (they are otherwise kept for the life of
+    the process so that a fit allocates nothing per iteration)."""
+    _workspaces.clear()
+    _ll_scratches.clear()
+    _km_workspaces.clear()
+
+
 _ll_scratches = {}
 
 
