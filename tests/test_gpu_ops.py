@@ -321,3 +321,65 @@ def test_large_n_properties(ops):
     want = orc.loglik(X[idx].cpu().numpy(), S[idx].cpu().numpy(), alpha.cpu().numpy(), mu.cpu().numpy(),
                       Sigma.cpu().numpy())
     assert np.max(np.abs(ll[idx].cpu().numpy() - want)) < 2e-4 * np.abs(want).max()
+
+
+@pytest.mark.parametrize("N,D,K", [(10_000_000, 10, 64), (12_500_000, 16, 128)])
+def test_full_size_properties(ops, N, D, K):
+    """BASELINE.json's FULL single-GPU sizes (configs[1]; the per-GPU shard of configs[4]), through properties that do
+    not need the oracle to hold the table: bit-reproducibility, additivity over shards, responsibilities summing to one
+    per point, agreement of the two passes and of the packed layout, EM monotonicity, and the oracle on two slices."""
+    from density_deconvolution_b200.synthetic import make_mixture, make_points
+    free = torch.cuda.mem_get_info(dev())[0]
+    if free < 2.2 * N * 4 * (D + D * D):
+        pytest.skip("not enough free device memory for this size")
+    alpha, mu, Sigma, q = make_mixture(D, K, seed=0, device=dev())
+    X, S = make_points(N, alpha, mu, q, seed=1)
+    la = alpha.log()
+    stats = torch.empty(ops.stats_len(D, K), dtype=torch.float32, device=dev())
+    ll, st = ops.estep_stats(X, S, la, mu, Sigma)
+    st = st.clone()
+    _, st_b = ops.estep_stats(X, S, la, mu, Sigma, want_ll=False, out_stats=stats)
+    assert torch.equal(st, st_b), "run-to-run deterministic at full size"
+    ref = st.double()
+    assert ref[-1].item() == 0 and ref[-2].item() == N
+    assert abs(ref[:K].sum().item() - N) < 1e-4 * N
+    # additivity over three unequal shards (what the multi-GPU all-reduce relies on)
+    cuts = [0, N // 3 + 1, 2 * (N // 3) + 7, N]
+    tot = torch.zeros_like(ref)
+    for lo, hi in zip(cuts, cuts[1:]):
+        _, s = ops.estep_stats(X[lo:hi], S[lo:hi], la, mu, Sigma, want_ll=False)
+        tot += s.double()
+    body = slice(0, K * (1 + D + D * D))
+    assert (tot[body] - ref[body]).abs().max() < 2e-5 * ref[body].abs().max()
+    assert abs((tot[-4] + tot[-3]) - (ref[-4] + ref[-3])) < 1e-7 * abs(ref[-4].item())
+    # the two passes, and the double sum against the float64 sum of the per-point values
+    ll_pass, sums = ops.loglik(X, S, la, mu, Sigma, want_sum=True)
+    assert torch.allclose(ll_pass, ll, rtol=3e-6, atol=3e-6)
+    assert abs(sums[0].item() - ll.double().sum().item()) < 1e-7 * abs(sums[0].item())
+    assert abs((ref[-4] + ref[-3]).item() - ll.double().sum().item()) < 1e-7 * abs(sums[0].item())
+    # oracle on two slices (start and ragged end)
+    for idx in (slice(0, 192), slice(N - 131, N)):
+        want = orc.loglik(X[idx].cpu().numpy(), S[idx].cpu().numpy(), alpha.cpu().numpy(), mu.cpu().numpy(),
+                          Sigma.cpu().numpy())
+        assert np.max(np.abs(ll[idx].cpu().numpy() - want)) < 2e-4 * np.abs(want).max()
+    del ll_pass
+    # packed layout on the first 2e6 points
+    n2 = 2_000_000
+    P = ops.pack_noise(S[:n2])
+    _, sp = ops.estep_stats(X[:n2], P, la, mu, Sigma, noise="packed", want_ll=False)
+    _, sf = ops.estep_stats(X[:n2], S[:n2], la, mu, Sigma, want_ll=False)
+    assert (sp - sf).abs().max().item() <= 2e-5 * sf.abs().max().item()
+    del P
+    # EM from a perturbed start: the log-likelihood never decreases (4 iterations, full table)
+    g = torch.Generator(device="cpu").manual_seed(3)
+    m = (mu.cpu() + 0.3 * torch.randn(K, D, generator=g)).to(dev())
+    Sg = (1.2 * Sigma).contiguous()
+    a, la2 = alpha.clone(), alpha.log()
+    trace = []
+    for _ in range(4):
+        ops.estep_stats(X, S, la2, m, Sg, want_ll=False, out_stats=stats)
+        trace.append((stats[-4].double() + stats[-3].double()).item())
+        assert stats[-1].item() == 0
+        ops.mstep_update(stats, N, 1e-3, m, Sg, a, la2)
+    assert all(b >= a_ - 1e-7 * abs(a_) for a_, b in zip(trace, trace[1:])), trace
+    assert abs(a.sum().item() - 1.0) < 1e-4
