@@ -21,6 +21,7 @@ _ERRORS = {
     -1: "bad argument", -2: "unsupported dimension D (1..32)", -3: "unsupported component count K (1..1024) for this call",
     -4: "workspace too small", -5: "unknown noise layout", -6: "no sm_100 CUDA device",
     -7: "out_ll is required for this shape (dgmm_stats_needs_ll)",
+    -8: "shape needs more scratch than the library's static array holds (use the entry point that takes a workspace)",
 }
 
 # every symbol include/dgmm_b200.h declares (tests check the list against the header)
@@ -32,6 +33,7 @@ SYMBOLS = (
     "dgmm_ctx_upload", "dgmm_em_iteration_resident", "dgmm_em_fit_resident", "dgmm_score_resident",
     "dgmm_pack_noise_f32", "dgmm_pack_noise_host",
     "dgmm_kmeans_workspace_bytes", "dgmm_kmeans_assign_f32", "dgmm_kmeans_update_f32",
+    "dgmm_kmeans_static_scratch_bytes", "dgmm_kmeans_assign_static_f32",
     "dgmm_gather_points_f32", "dgmm_posterior_sample_f32", "dgmm_posterior_logprob_f32", "dgmm_sgd_params_f32", "dgmm_sgd_adam_step_f32", "dgmm_sgd_fused_step_f32", "dgmm_sgd_adam_step_peers_f32",
     "dgmm_debug_set_tuning", "dgmm_debug_get_plan", "dgmm_debug_pair_timing", "dgmm_debug_pair_times",
 )
@@ -117,6 +119,10 @@ def lib():
     L.dgmm_kmeans_workspace_bytes.argtypes = [i32, i32]
     L.dgmm_kmeans_assign_f32.restype = i32
     L.dgmm_kmeans_assign_f32.argtypes = [vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
+    L.dgmm_kmeans_static_scratch_bytes.restype = sz
+    L.dgmm_kmeans_static_scratch_bytes.argtypes = []
+    L.dgmm_kmeans_assign_static_f32.restype = i32
+    L.dgmm_kmeans_assign_static_f32.argtypes = [vp, i64, i32, i32, vp, vp, vp, vp]
     L.dgmm_kmeans_update_f32.restype = i32
     L.dgmm_kmeans_update_f32.argtypes = [i32, vp, i32, i32, vp, vp, vp]
     L.dgmm_gather_points_f32.restype = i32

@@ -300,6 +300,28 @@ assign_fn assign_entry() { return &kmeans_assign_kernel<D>; }
 const assign_fn kAssign[DGMM_MAX_D + 1] = {nullptr,     KM_ROW4(1),  KM_ROW4(5),  KM_ROW4(9), KM_ROW4(13),
                                            KM_ROW4(17), KM_ROW4(21), KM_ROW4(25), KM_ROW4(29)};
 
+// ---- scratch of the allocation-free entry point (dgmm_kmeans_assign_static_f32) -----------------------------------
+// A file-scope device array: every GPU that loads the library holds these 8 MiB until the process exits.  In HOST code
+// the name `g_km_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device with cudaGetSymbolAddress (that device current) and cached.
+constexpr size_t kKmStaticBytes = (size_t)8 << 20;
+static __device__ __align__(256) unsigned char g_km_scratch[kKmStaticBytes];
+
+int km_static_scratch(void** out) {
+    static void* cache[64] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DGMM_ERR_NO_DEVICE;
+    if (!cache[dev]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_km_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!ptr) return DGMM_ERR_NO_DEVICE;
+        cache[dev] = ptr;
+    }
+    *out = cache[dev];
+    return 0;
+}
+
 int km_device(int* sms, int* smem_optin) {
     int dev = 0, major = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return DGMM_ERR_NO_DEVICE;
@@ -348,6 +370,26 @@ int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, const float*
     kmeans_finalize_kernel<<<(total + 7) / 8, 256, 0, st>>>(ws.part, ws.part_d, grid, D, K, out_stats);
     CUDA_TRY(cudaGetLastError());
     return 0;
+}
+
+size_t dgmm_kmeans_static_scratch_bytes(void) { return kKmStaticBytes; }
+
+// dgmm_kmeans_assign_f32 with its workspace in the library's own static device array: no cudaMalloc / cudaFree / allocating
+// routine anywhere on this path.  Shapes whose workspace (dgmm_kmeans_workspace_bytes) exceeds the array are rejected.
+// All calls on a device share the array: calls that overlap on the GPU (two streams) race.  Nothing in it has to start at
+// zero: every partial the finalise kernel reads is written by the assignment kernel of the same call.
+int dgmm_kmeans_assign_static_f32(const float* X, int64_t N, int D, int K, const float* centroids, int32_t* labels,
+                                  float* out_stats, void* stream) {
+    if (D < 1 || D > DGMM_MAX_D) return DGMM_ERR_UNSUPPORTED_D;
+    if (K < 1 || K > DGMM_MAX_K) return DGMM_ERR_UNSUPPORTED_K;
+    int sms = 0, optin = 0;
+    int rc = km_device(&sms, &optin);
+    if (rc) return rc;
+    if (km_carve(nullptr, D, K, sms).bytes > kKmStaticBytes) return DGMM_ERR_STATIC_SCRATCH;
+    void* scratch = nullptr;
+    rc = km_static_scratch(&scratch);
+    if (rc) return rc;
+    return dgmm_kmeans_assign_f32(X, N, D, K, centroids, labels, out_stats, scratch, kKmStaticBytes, stream);
 }
 
 int dgmm_gather_points_f32(const float* X, const float* S, int noise_layout, const int64_t* idx, int64_t B, int D,

@@ -53,6 +53,7 @@ extern "C" {
 #define DGMM_ERR_WORKSPACE (-4)      /* workspace too small / null                      */
 #define DGMM_ERR_LAYOUT (-5)         /* unknown noise layout                            */
 #define DGMM_ERR_NO_DEVICE (-6)      /* no CUDA device / not an sm_100 part             */
+#define DGMM_ERR_STATIC_SCRATCH (-8) /* shape needs more scratch than the static array of a *_static_* entry point holds */
 #define DGMM_ERR_LL_REQUIRED (-7)    /* dgmm_estep_stats_f32 needs out_ll for this shape (dgmm_stats_needs_ll) */
 
 /* noise-covariance layouts (the reference contract is DGMM_NOISE_FULL:
@@ -243,6 +244,18 @@ DGMM_API size_t dgmm_kmeans_workspace_bytes(int D, int K);
 DGMM_API int dgmm_kmeans_assign_f32(const float* X, int64_t N, int D, int K, const float* centroids,
                                     int32_t* labels, float* out_stats, void* workspace, size_t workspace_bytes,
                                     void* stream);
+
+/* dgmm_kmeans_assign_f32 for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc): same inputs, outputs and results, but the per-block partial sums live in a file-scope
+ * `static __device__` array of the library (dgmm_kmeans_static_scratch_bytes() = 8 MiB, held by every GPU that loads the
+ * library until the process exits) instead of a caller-provided workspace; the call makes no cudaMalloc / cudaFree /
+ * allocating library call.  Limit: shapes with dgmm_kmeans_workspace_bytes(D, K) > 8 MiB (on a 148-SM B200:
+ * K * ceil((D + 1) / 4) > 442, e.g. K > 147 at D = 10, K > 88 at D = 16) return DGMM_ERR_STATIC_SCRATCH.  All calls on a
+ * device share the array: calls that overlap on the GPU (different streams) race; calls on one stream are safe.
+ * No counterpart in the reference. */
+DGMM_API size_t dgmm_kmeans_static_scratch_bytes(void);
+DGMM_API int dgmm_kmeans_assign_static_f32(const float* X, int64_t N, int D, int K, const float* centroids,
+                                           int32_t* labels, float* out_stats, void* stream);
 
 /* Centroid update from the (all-reduced) packed buffer, in place.
  *   mode 0, Lloyd (deconv/gmm/util.py:23-24): c_j = sums_j / counts_j; an empty cluster keeps its
