@@ -41,7 +41,7 @@ struct AdamCfg {
 // statistic they need from ALL peers' buffers and add the `world` values themselves, in rank order (bit-identical
 // on every rank).  Hand-shake: after its finalise kernel a rank stamps flag[rank] in every peer's buffer
 // (st.release.sys after a system fence); a consumer block spins (bounded) until all `world` local flags carry the
-// step's stamp (ld.acquire.sys) before its first peer read.  Buffers alternate with the step parity, so a fast rank
+// step's stamp (ld.acquire.sys, bounded at ~20 s) before its first peer read.  Buffers alternate with the step parity, so a fast rank
 // can never overwrite statistics a slow one is still reading (it cannot get two steps ahead: its next hand-shake
 // needs the slow rank's stamp).
 constexpr int kMaxPeers = 8;
@@ -78,7 +78,7 @@ __device__ __forceinline__ void peer_wait(const PeerView& pv) {
     if ((int)threadIdx.x < pv.world) {
         const long long t0 = clock64();
         while ((int)(ld_acquire_sys(pv.flags + threadIdx.x) - pv.stamp) < 0) {
-            if (clock64() - t0 > 4000000000LL) {   // ~2 s at 1.9 GHz: a peer is gone; do not hang the GPU
+            if (clock64() - t0 > 40000000000LL) {   // ~20 s at 1.9 GHz: a peer is gone; do not hang the GPU
                 if (pv.timeout) *pv.timeout = 1;
                 break;
             }

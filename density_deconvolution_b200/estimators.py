@@ -743,6 +743,15 @@ class BaseSGDGMM:
             st["step"].fill_(float(step))
         self.optimiser._opt_called = True   # what optimiser.step() records for the lr scheduler's order check
         acc = epoch_acc.cpu()
+        peers = getattr(self, "_peers", None)
+        if peers is not None and _dist.is_distributed():
+            # every rank's last Adam kernel has read its peers' buffers before anybody moves on (and could free one);
+            # a peer that never published its statistics within the kernels' bounded wait is an error of its own
+            timed_out = bool(peers.timeout.item())
+            torch.distributed.barrier()
+            if timed_out:
+                raise _ops.DgmmError("fused cross-GPU reduction: a peer rank did not publish its statistics within the "
+                                     "time limit (is every rank running the same number of minibatch steps?)")
         if acc[1].item() > 0:
             return math.nan
         return acc[0].item() / n_total

@@ -353,7 +353,7 @@ DGMM_API int dgmm_sgd_fused_step_f32(const float* X, const float* S, int noise_l
  * of device pointers) is rank r's buffer as mapped in this process.  Layout in floats: this step's packed statistics
  * at stats_off (callers alternate two regions with the step parity), `world` uint32 hand-shake flags at flags_off.
  * The local statistics must already be in peer_bufs[rank] + stats_off (same stream).  The call stamps flag[rank] = stamp
- * in every peer's buffer (release, system scope); the Adam kernels wait (bounded, ~2 s) for all `world` local flags to
+ * in every peer's buffer (release, system scope); the Adam kernels wait (bounded, ~20 s) for all `world` local flags to
  * reach `stamp` (acquire), then read each statistic from all peers and add them in rank order - bit-identical on
  * every rank.  stamp must grow by one per step.  timeout_flag (device int, zeroed by the caller) is set when a peer
  * never answered; epoch_acc[1] is then poisoned like a non-PD pair. */
