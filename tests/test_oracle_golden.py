@@ -198,3 +198,40 @@ def test_non_pd_returns_minus_inf():
     S = np.tile(np.diag([1.0, -5.0]), (2, 1, 1))
     ll, e, _ = orc.e_step(X, S, np.ones(1), np.zeros((1, 2)), np.eye(2)[None])
     assert ll == -math.inf and e is None
+
+
+# ---- real tables (BASELINE.json configs[2], configs[3]): the oracle tracks the reference's EM iterations ------------
+def _real_noise(seed, N, D):
+    """Same draw as tests/golden/make_golden.py::real_noise (S only)."""
+    rng = np.random.default_rng(seed)
+    Q = (0.5 / np.sqrt(D)) * rng.standard_normal((N, D, D))
+    return np.einsum("nba,nbc->nac", Q, Q) + 1e-3 * np.eye(D)
+
+
+def _tril_unpack(P, D):
+    ia, ib = np.tril_indices(D)
+    C = np.zeros(P.shape[:-1] + (D, D))
+    C[..., ia, ib] = P
+    C[..., ib, ia] = P
+    return C
+
+
+@pytest.mark.parametrize("name,iters", [("ref_wine_k128_f64.npz", 5), ("ref_ionosphere_k256_f64.npz", 5)])
+def test_oracle_tracks_reference_em_on_the_real_tables(name, iters):
+    """Injected init in the reference's style (alpha = 1/K, mu = K data rows, Sigma = I), full per-point noise, w = 1e-3:
+    log-likelihood trace and parameters after 1 and 5 iterations of the float64 reference (stored as float32)."""
+    g = golden(name)
+    X = g["X64"]
+    N, D = X.shape
+    K = int(g["K"])
+    S = _real_noise(int(g["seed"]), N, D)
+    alpha, mu, Sigma = np.full(K, 1.0 / K), X[g["rows"]].copy(), np.tile(np.eye(D), (K, 1, 1))
+    for it in range(1, iters + 1):
+        s0, s1, S2, ll = orc.suff_stats(X, S, alpha, mu, Sigma)
+        assert abs(ll.sum() - g["ll_trace"][it - 1]) <= 1e-9 * abs(g["ll_trace"][it - 1])
+        w_new, mu, Sigma = orc.m_step_from_stats(s0, s1, S2, mu, Sigma, N, float(g["w"]))
+        alpha = w_new[:, 0]
+        if "it%d_means" % it in g.files:
+            assert rel(alpha, g["it%d_weights" % it]) < 1e-6
+            assert rel(mu, g["it%d_means" % it]) < 1e-6
+            assert rel(Sigma, _tril_unpack(g["it%d_covars_tril" % it].astype(np.float64), D)) < 1e-6
