@@ -1345,7 +1345,9 @@ int dgmm_estep_full_f32(const float* X, const float* S, int noise_layout, int64_
         const long long blocks = ((long long)N + 127) / 128 * K;
         if (blocks > 0x7fffffffLL) return DGMM_ERR_BAD_ARG;
         void* args[] = {&f};
-        CUDA_TRY(cudaLaunchKernel(k, dim3((unsigned)blocks), dim3(128), args, 0, st));
+        const size_t dyn = out_B ? full_dyn_smem_bytes(D) : 0;
+        if (dyn > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        CUDA_TRY(cudaLaunchKernel(k, dim3((unsigned)blocks), dim3(128), args, dyn, st));
     }
     if (status) {
         finalize_ll_kernel<<<1, 32, 0, st>>>(ws.part_ll, ws.nonpd, nblk, nullptr, status, 0);

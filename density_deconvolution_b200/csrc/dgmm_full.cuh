@@ -12,7 +12,17 @@
 #include "dgmm_core.cuh"
 #include "dgmm_pair.cuh"
 
+// Largest D whose materialising E-step forms B_ij = Sigma_j - V^T V from V = L^{-1} Sigma_j in registers
+#ifndef DGMM_FULL_V_D
+#define DGMM_FULL_V_D 10
+#endif
+
 namespace dgmm {
+
+// dynamic shared memory of full_kernel<D>: the per-warp D x D staging tiles of the small-D route
+__host__ __device__ constexpr size_t full_dyn_smem_bytes(int D) {
+    return D <= DGMM_FULL_V_D ? (size_t)4 * 32 * ((D * D) | 1) * sizeof(float) : 0;
+}
 
 struct FullParams {
     const float* X;
