@@ -21,7 +21,8 @@ namespace dgmm {
 
 // dynamic shared memory of full_kernel<D>: the per-warp D x D staging tiles of the small-D route
 __host__ __device__ constexpr size_t full_dyn_smem_bytes(int D) {
-    return D <= DGMM_FULL_V_D ? (size_t)4 * 32 * ((D * D) | 1) * sizeof(float) : 0;
+    return D <= DGMM_FULL_V_D ? (size_t)4 * 32 * ((D * D) | 1) * sizeof(float)
+           : (D <= DGMM_UNROLL_D ? (size_t)D * ((D + 3) & ~3) * 128 * sizeof(float) : 0);   // D = 11..16: V per thread
 }
 
 struct FullParams {
