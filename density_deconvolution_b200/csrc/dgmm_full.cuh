@@ -16,6 +16,11 @@
 #ifndef DGMM_FULL_V_D
 #define DGMM_FULL_V_D 10
 #endif
+// resident blocks per SM of that variant: 3 x 128 threads at <= 168 registers (48 bytes of spills at D = 10) beat 2 at 198
+// (gpurun A/B at the c2 shape: 1.02 -> 0.95 ms)
+#ifndef DGMM_FULL_MINB
+#define DGMM_FULL_MINB 3
+#endif
 
 namespace dgmm {
 
