@@ -799,7 +799,8 @@ class BaseSGDGMM:
             if tim and es_tl is not None and sign * train_loss < es_tl:          # sgd_gmm_tim.py:187-189
                 break
             if val_data:
-                val_loss = self.score_batch(val_data) / _global_count(len(val_data), self.device)
+                n_val = as_tensors(val_data)[0].shape[0]                         # len(val_data), also for (X, S) tuples
+                val_loss = self.score_batch(val_data) / _global_count(n_val, self.device)
                 self.val_loss_curve.append(sign * val_loss)
             if not tim:
                 self.scheduler.step()                                            # disabled in the fork (:195)
