@@ -537,13 +537,15 @@ int make_plan(const DeviceInfo& dev, int mode, int D, int K, long long N, int no
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, p.kernel, p.TPB, p.smem));
     if (occ < 1) return DGMM_ERR_UNSUPPORTED_K;
     p.tmem_cols = 0;
-    if (mode == MODE_STATS && p.accp == ST_TMEM) {
+    const bool sig_tmem = (v.sigp == ST_TMEM);
+    if ((mode == MODE_STATS && p.accp == ST_TMEM) || sig_tmem) {
         // The occupancy query answers 1 block/SM for any kernel that allocates tensor memory, yet
         // blocks whose columns fit side by side do run concurrently (tools/ubench_tmem.cu): derive
         // the residency from registers, shared memory and the 512 TMEM columns instead.  All
         // resident blocks must hold their columns at the same time (a block that cannot allocate
         // would spin until another one exits).
-        p.tmem_cols = tmem_alloc_cols(ns_of(D), p.TPB / 32);
+        p.tmem_cols = tmem_alloc_cols(sig_tmem ? nd_of(D) : ns_of(D), p.TPB / 32);
+        if (p.tmem_cols > 512) return DGMM_ERR_UNSUPPORTED_K;
         cudaFuncAttributes fa;
         CUDA_TRY(cudaFuncGetAttributes(&fa, p.kernel));
         const int regs_per_block = ((fa.numRegs + 7) & ~7) * p.TPB;

@@ -87,7 +87,7 @@ inline PairVariant pair_by_gcls(int gcls, int nz) {
 //   D = 11, 12   : accumulators in tensor memory, 4 resp. 3 blocks/SM  [D=12: 0.59 vs 0.50 registers]
 //   13 <= D <= 16: Sigma_j in shared-memory columns, accumulators in tensor memory, 255 registers,
 //                  2 blocks/SM       [D=16,K=128: 0.61 vs 0.44 with shared-memory accumulators]
-//   LOGLIK       : Sigma_j in shared-memory columns; 128 registers x 4 blocks/SM (D <= 12), 255 above
+//   LOGLIK       : D <= 12: Sigma_j in shared-memory columns, 3 blocks/SM; D = 13..16: Sigma_j in tensor memory, 255 registers
 //   D = 17..24   : K >= 64: as 13..16 (unrolled, a few spilled words; Sigma_j through L1 when its columns
 //                  would leave one block per SM, and for K > 128); otherwise the fallback
 //   D = 21..32, and D = 17..20 with K < 64: the cooperative 8-lane-team kernels (dgmm_team.cuh)
@@ -124,6 +124,11 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
         if (nz == NZ_PACKED) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
         if constexpr (D <= 12) {
             if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 4>(gcls, nz);
+        } else if constexpr (D <= DGMM_UNROLL_D) {
+            // D = 13..16 log-likelihood pass with the Sigma_j columns in shared memory (the placement before tensor memory)
+            // (one variant, for A/B runs: K = 64..128, full noise)
+            if (mode == MODE_LOGLIK && gcls == GCLS_MW4 && nz == NZ_FULL)
+                return pair_variant<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, GCLS_MW4, NZ_FULL, kPairMaxThreads, 1>();
         } else if constexpr (D > DGMM_UNROLL_D && D <= DGMM_PAIR_UNROLL_D) {
             // Sigma_j through L1 instead of shared-memory columns: the planner takes this one when the
             // columns would leave room for only one block per SM (two blocks of 4 warps beat one)
@@ -144,6 +149,10 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
         }
         return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_REG, 128, 3>(gcls, nz);
     } else if constexpr (D <= DGMM_UNROLL_D) {
+        // log-likelihood pass: Sigma_j column in the thread's tensor-memory row (tcgen05.ld: 9 x16-loads per point at D = 16
+        // instead of 34 LDS.128; D=16,K=128: 21.5 -> 18.4 ms per 3e6 points, bit-identical); sub-warp groups keep shared memory
+        if (mode == MODE_LOGLIK && gcls != GCLS_SUB)
+            return pair_by_gcls<D, MODE_LOGLIK, ST_TMEM, ST_GLOBAL, kPairMaxThreads, 1>(gcls, nz);
         if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, kPairMaxThreads, 1>(gcls, nz);
         if (gcls != GCLS_SUB) return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_TMEM, kPairMaxThreads, 1>(gcls, nz);
         return pair_by_gcls<D, MODE_STATS, ST_GLOBAL, ST_SMEM, kPairMaxThreads, 1>(gcls, nz);
