@@ -87,7 +87,8 @@ inline PairVariant pair_by_gcls(int gcls, int nz) {
 //   D = 11, 12   : accumulators in tensor memory, 4 resp. 3 blocks/SM  [D=12: 0.59 vs 0.50 registers]
 //   13 <= D <= 16: Sigma_j in shared-memory columns, accumulators in tensor memory, 255 registers,
 //                  2 blocks/SM       [D=16,K=128: 0.61 vs 0.44 with shared-memory accumulators]
-//   LOGLIK       : D <= 12: Sigma_j in shared-memory columns, 3 blocks/SM; D = 13..16: Sigma_j in tensor memory, 255 registers
+//   LOGLIK       : D <= 6: Sigma_j in shared-memory columns + refill, 3 blocks/SM; D = 7..12: Sigma_j in tensor memory,
+//                  3 blocks/SM; D = 13..16: Sigma_j in tensor memory, 255 registers
 //   D = 17..24   : K >= 64: as 13..16 (unrolled, a few spilled words; Sigma_j through L1 when its columns
 //                  would leave one block per SM, and for K > 128); otherwise the fallback
 //   D = 21..32, and D = 17..20 with K < 64: the cooperative 8-lane-team kernels (dgmm_team.cuh)
@@ -123,7 +124,9 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
     if (which == 1) {  // alternative placements (tuning sweeps, tools/gpu_ab.sh); not compiled for packed noise
         if (nz == NZ_PACKED) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
         if constexpr (D <= 12) {
-            if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 4>(gcls, nz);
+            // (one variant, for A/B runs: the shared-memory / in-factorisation-refill placement that D >= 7 left)
+            if (mode == MODE_LOGLIK && gcls == GCLS_MW4 && nz == NZ_FULL && D >= 7)
+                return pair_variant<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, GCLS_MW4, NZ_FULL, 128, 3>();
         } else if constexpr (D <= DGMM_UNROLL_D) {
             // D = 13..16 log-likelihood pass with the Sigma_j columns in shared memory (the placement before tensor memory)
             // (one variant, for A/B runs: K = 64..128, full noise)
@@ -141,6 +144,11 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
     // Accumulators in tensor memory need warp-uniform control flow: sub-warp groups (K < 32) keep
     // the register / shared-memory placements.
     if constexpr (D <= 12) {
+        // log-likelihood pass, D = 7..12: Sigma_j column in tensor memory, no in-factorisation refill (gpurun A/B against the
+        // shared-memory + refill placement: D=9,K=128 +9 %, D=10,K=64 +7 %, D=12,K=128 +9 %); D <= 6 and sub-warp groups keep it
+        if constexpr (D >= 7) {
+            if (mode == MODE_LOGLIK && gcls != GCLS_SUB) return pair_by_gcls<D, MODE_LOGLIK, ST_TMEM, ST_GLOBAL, 128, 3>(gcls, nz);
+        }
         if (mode == MODE_LOGLIK) return pair_by_gcls<D, MODE_LOGLIK, ST_SMEM, ST_GLOBAL, 128, 3>(gcls, nz);
         if constexpr (D == 11) {
             if (gcls != GCLS_SUB) return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_TMEM, 128, 4>(gcls, nz);
