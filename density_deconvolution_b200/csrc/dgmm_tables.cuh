@@ -60,6 +60,20 @@ inline PairVariant pair_wide_unrolled(int gcls, int nz, bool sigma_global = fals
     return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
 }
 
+// D = 17..20 log-likelihood pass: Sigma_j column (up to 210 floats) in the thread's tensor-memory row instead of global
+// memory through L1 (K = 64..128: two 128-thread blocks per SM of 256 columns each; K = 129..256: one 256-thread block).
+template <int D>
+inline PairVariant pair_wide_loglik_tmem(int gcls, int nz) {
+    if (gcls == GCLS_MW4) {
+        if (nz == NZ_FULL) return pair_variant_wide_unrolled<D, MODE_LOGLIK, ST_TMEM, ST_GLOBAL, GCLS_MW4, NZ_FULL>();
+        if (nz == NZ_DIAG) return pair_variant_wide_unrolled<D, MODE_LOGLIK, ST_TMEM, ST_GLOBAL, GCLS_MW4, NZ_DIAG>();
+    } else if (gcls == GCLS_MWN) {
+        if (nz == NZ_FULL) return pair_variant_wide_unrolled<D, MODE_LOGLIK, ST_TMEM, ST_GLOBAL, GCLS_MWN, NZ_FULL>();
+        if (nz == NZ_DIAG) return pair_variant_wide_unrolled<D, MODE_LOGLIK, ST_TMEM, ST_GLOBAL, GCLS_MWN, NZ_DIAG>();
+    }
+    return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
+}
+
 // The four group classes of one placement.  Groups wider than 128 lanes (GCLS_MWN) need blocks of
 // 256 threads, so that class is always compiled with the (256, 1) bounds.
 template <int D, int MODE, int SIGP, int ACCP, int NZ, int MAXT, int MINB>
@@ -135,7 +149,9 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
         } else if constexpr (D > DGMM_UNROLL_D && D <= DGMM_PAIR_UNROLL_D) {
             // Sigma_j through L1 instead of shared-memory columns: the planner takes this one when the
             // columns would leave room for only one block per SM (two blocks of 4 warps beat one)
-            if (mode == MODE_LOGLIK) return pair_wide_unrolled<D, MODE_LOGLIK, ST_GLOBAL>(gcls, nz, true);
+            if (mode == MODE_LOGLIK && gcls == GCLS_MW4 && nz == NZ_FULL)   // (A/B: Sigma_j through L1, the placement before)
+                return pair_variant_wide_unrolled<D, MODE_LOGLIK, ST_GLOBAL, ST_GLOBAL, GCLS_MW4, NZ_FULL>();
+            if (mode == MODE_LOGLIK) return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
             if constexpr (D <= 20) return pair_wide_unrolled<D, MODE_STATS, ST_TMEM>(gcls, nz, true);
         }
         return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
@@ -165,7 +181,7 @@ inline PairVariant pair_lookup(int mode, int which, int gcls, int nz) {
         if (gcls != GCLS_SUB) return pair_by_gcls<D, MODE_STATS, ST_SMEM, ST_TMEM, kPairMaxThreads, 1>(gcls, nz);
         return pair_by_gcls<D, MODE_STATS, ST_GLOBAL, ST_SMEM, kPairMaxThreads, 1>(gcls, nz);
     } else if constexpr (D <= DGMM_PAIR_UNROLL_D) {
-        if (mode == MODE_LOGLIK) return pair_wide_unrolled<D, MODE_LOGLIK, ST_GLOBAL>(gcls, nz);
+        if (mode == MODE_LOGLIK) return pair_wide_loglik_tmem<D>(gcls, nz);
         return pair_wide_unrolled<D, MODE_STATS, ST_TMEM>(gcls, nz);
     }
     return PairVariant{nullptr, 0, 0, 0, 0, 0, 0};
